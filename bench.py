@@ -1,0 +1,244 @@
+#!/usr/bin/env python
+"""bench.py -- agent-steps/s of the Battlespace hot path on B200 (BASELINE.json metric).
+
+Workload (BASELINE.json configs[2], the configuration the metric is quoted on): 3v3, continuous
+actions, cf.json rewards, red = uniform[-1,1]^3 actions, blue = instinct team, 65,536 envs per GPU,
+one "step" = one fused launch of T=32 ticks that also writes the MADDPG replay rows into a 2^20-row
+device ring (bs_rollout_fused).  Weak scaling: every GPU owns 65,536 envs (global env index keys the
+Philox streams), no collective on the step path, one NCCL all-reduce of the 8 statistics counters
+per report interval (= once per timed region).
+
+  value : kernel-path throughput, state/actions resident in HBM (red actions drawn in-kernel)
+  e2e   : same metric through the host-buffer C-ABI call bs_rollout_fused_host: every step copies
+          the red team's actions [T,E,3,3] float32 from pinned host memory and reads the 8 counters back
+  roofline / cpu_baseline : see DESIGN.md section "Measurement"
+
+`--impl reference` times the CPU implementation of the same path on the host cores.  The reference
+itself is pure Python and its tree is not present on the GPU box, so that arm runs the C port in
+oracle/ (bit-exact against the reference, see tests/test_oracle_golden.py) on all host threads.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "deep-rl-battlespace_b200"))
+
+N_AGENTS, T_TICKS, ENVS_PER_GPU, RING_ROWS = 3, 32, 65536, 1 << 20
+REWARDS = dict(hit_base_reward=1.0, hit_plane_reward=0.9, miss_punishment=-0.02, die_punishment=-0.03,
+               lose_punishment=-0.05)  # main.py:33-37 / models/completed_model/cf.json
+METRIC, UNIT = "agent-steps/sec (3v3 vs instinct)", "agent-steps/s"
+
+
+def algorithmic_bytes_per_env_tick(N, A, T, actions_from_hbm):
+    """SURVEY.md 8(d), Mode B: replay row + amortised state read/write (+ action read)."""
+    L = 3 * N + 2
+    row = 2 * N * L * 4 + N * A * 4 + N * 4 + N          # state, new_state, action, reward, done
+    S = 218 * N + 16                                      # per-env state bytes
+    return row + 2 * S / T + (N * A * 4 if actions_from_hbm else 0)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_port_rate(steps, warmup, envs, threads=None):
+    """agent-steps/s of the CPU port (oracle/) on the same workload, all host threads."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    cores = threads or os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    from port import OracleEnv, POL_INSTINCT, POL_RANDOM
+    env = OracleEnv(N_AGENTS, True, tuple(REWARDS.values()), envs, seed=0)
+    for _ in range(warmup):
+        env.rollout(T_TICKS, [POL_RANDOM, POL_INSTINCT])
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        env.rollout(T_TICKS, [POL_RANDOM, POL_INSTINCT])
+    dt = time.perf_counter() - t0
+    return steps * T_TICKS * envs * 2 * N_AGENTS / dt, dt, cores
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    envs = args.ref_envs
+    rate, dt, cores = cpu_port_rate(args.steps, args.warmup, envs)
+    sample = f"{envs} envs x {T_TICKS} ticks per step, {args.steps} steps ({dt:.1f} s), OpenMP over envs"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "3v3 continuous, red=uniform random, blue=instinct, fused 32-tick rollout + replay rows "
+                               "(CPU port of the reference tick; the Python reference tree is absent on this box)",
+                   "envs": envs, "ticks_per_step": T_TICKS},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs", type=int, default=ENVS_PER_GPU, help="envs per GPU")
+    ap.add_argument("--ref-envs", type=int, default=2048, help="envs per step of the CPU arm")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        return run_reference(args, rank)
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    from battlespace import DeviceReplay, allreduce_stats, parallel_env
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    N, T, E, A = N_AGENTS, T_TICKS, args.envs, 3
+    env = parallel_env(n_agents=N, continuous_actions=True, n_envs=E, env_offset=rank * E, seed=0, device=dev, **REWARDS)
+    replay = DeviceReplay(RING_ROWS, 512, N, 3 * N + 2, A, dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- kernel path: everything resident in HBM ------------------------------------------------
+    for _ in range(args.warmup):
+        env.rollout(T, "random", "instinct", 0, None, replay)
+    barrier()
+    clocks = ClockSampler(local) if rank == 0 else None
+    if clocks:
+        clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        env.rollout(T, "random", "instinct", 0, None, replay)     # one kernel launch per step
+    stats_dev = allreduce_stats(env.stats_tensor())                # the report-interval all-reduce (NCCL)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clk = clocks.stop() if clocks else None
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    agent_steps = args.steps * T * E * 2 * N * world
+    value = agent_steps / (ms * 1e-3)
+    totals = stats_dev.cpu().numpy()
+
+    # ---- e2e: host-buffer C-ABI call, red actions copied from pinned host memory each step ------
+    e2e = None
+    if not args.no_e2e:
+        k_e2e = max(3, min(args.steps, 40))
+        host_act = torch.empty((T, E, N, A), dtype=torch.float32).uniform_(-1, 1).pin_memory()
+        for _ in range(3):
+            env.rollout_host(T, "external", "instinct", 0, host_act, replay)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k_e2e):
+            env.rollout_host(T, "external", "instinct", 0, host_act, replay)   # H2D + kernel + D2H, synchronous
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e = {"value": k_e2e * T * E * 2 * N * world / float(tt.item()), "unit": UNIT,
+               "h2d_bytes_per_step": T * E * N * A * 4, "d2h_bytes_per_step": 64, "steps": k_e2e,
+               "call": "bs_rollout_fused_host (red actions [T,E,3,3] f32 from pinned host memory, counters back)"}
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        bytes_per_launch = algorithmic_bytes_per_env_tick(N, A, T, False) * T * E
+        launch_s = ms * 1e-3 / args.steps
+        achieved = bytes_per_launch / launch_s / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("rollout_kernel_dram_bytes_per_launch")
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            rate, dt, cores = cpu_port_rate(6, 2, 2048)
+            cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": f"2048 envs x {T} ticks x 6 steps ({dt:.1f} s) of the same workload, OpenMP over envs"}
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "BASELINE configs[2]: 3v3 continuous, red=Philox uniform[-1,1]^3 in-kernel, "
+                                   "blue=instinct in-kernel, fused T=32 ticks/launch writing replay rows",
+                       "envs_per_gpu": E, "ticks_per_step": T, "replay_ring_rows": RING_ROWS, "rewards": "cf.json",
+                       "parallelism": f"env-sharded x{world}, no step-path collective, 1 stats all-reduce/interval",
+                       "l2": "inputs+outputs per launch (0.75 GB: 0.66 GB replay rows written, 44 MB state) exceed the "
+                             "126 MB L2; no explicit flush"},
+            "e2e": e2e, "gpu_launches": args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src, "kernel": "rollout_kernel<3,true>",
+                         "algorithmic_bytes_per_launch": bytes_per_launch, "launch_ms": launch_s * 1e3},
+            "cpu_baseline": cpu, "clocks": clk,
+            "stats": {"games": int(totals[3]), "red_wins": int(totals[0]), "blue_wins": int(totals[1]),
+                      "ties": int(totals[2]), "agent_steps_counted": int(totals[7])},
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,754 @@
+// battlespace.cu -- kernels + C ABI (include/battlespace.h) of libbattlespace.so, sm_100a only.
+//
+// Kernels (all use the lane-per-plane mapping of tick.cuh):
+//   reset_kernel     parallel_env.reset for masked envs              battle_env.py:246-279
+//   step_kernel      one tick, actions from HBM and/or in-kernel policies   battle_env.py:281-381
+//   rollout_kernel   T fused ticks + auto-reset + replay rows        main.py:178-213, maddpg/buffer.py:25-47
+//   instinct_kernel  instinct Team.choose_actions on an obs tensor   instinct/agent.py:10-62
+// There is no CPU path in this library.
+#include "../../include/battlespace.h"
+#include "tick.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace bs;
+
+// ------------------------------------------------------------------------------------------------
+// kernels
+// ------------------------------------------------------------------------------------------------
+constexpr int BLOCK = 128;
+
+__device__ __forceinline__ long long global_warp() {
+    return ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+}
+
+__device__ __forceinline__ double clip1(double v) { return v < -1 ? -1 : (v > 1 ? 1 : v); }  // battle_env.py:295-297
+
+__device__ __forceinline__ int argmax4(const float *v) {  // np.argmax: first maximum, battle_env.py:328
+    int b = 0;
+    float m = v[0];
+#pragma unroll
+    for (int c = 1; c < 4; ++c) if (v[c] > m) { m = v[c]; b = c; }
+    return b;
+}
+
+template <int N>
+__global__ void __launch_bounds__(BLOCK) reset_kernel(Params p, const uint8_t *mask, const int32_t *draws, float *obs) {
+    constexpr int P = 2 * N, L = 3 * N + 2;
+    Geo<N> g(global_warp(), p.E);
+    Lane<N> s;
+    double ret0, ret1;
+    load_lane(p, g, s, ret0, ret1);
+    const bool need = g.valid && (mask == nullptr || mask[g.e] != 0);
+    if (need) {
+        reset_lane(p, g, s, draws != nullptr, draws ? draws + g.e * (4 + 6 * N) : nullptr);
+        ret0 = ret1 = 0;
+    }
+    gather(g, s);
+    if (obs != nullptr) {
+        float o[L];
+        observe<N>(p, s, o);
+        if (g.valid) {
+            float *dst = obs + (g.e * P + g.i) * L;
+#pragma unroll
+            for (int c = 0; c < L; ++c) dst[c] = o[c];
+        }
+    }
+    if (need) store_lane(p, g, s, ret0, ret1, true);
+}
+
+struct StepArgs {
+    const void *actions;  // layout [E, act_agents, ...]
+    int dtype;
+    int act_agents;       // 2N (both teams external) or N (act_team only)
+    int act_team;
+    int pol[2];           // per team: POL_*
+    const double *draws;  // null or [E,2N,5]
+    float *obs, *rew;
+    uint8_t *done, *env_done;
+    int8_t *winner;
+};
+
+// Decode the lane's policy into (adisc, a[3], spread_u).  o = the lane's current observation
+// (only read by the instinct policies).  raw[4] = the action row a replay buffer would store.
+template <int N, bool CONT>
+__device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, const Lane<N> &s, int pol,
+                                            const float (&o)[3 * N + 2], const double *draws_row,
+                                            int &adisc, double (&a)[3], double &spread_u, float (&raw)[4]) {
+    double u[5];
+    uint32_t w[4] = {0, 0, 0, 0};
+    if (draws_row != nullptr) {
+#pragma unroll
+        for (int c = 0; c < 5; ++c) u[c] = draws_row[c];
+    } else {
+        env_philox(p, g.e, s.episode, s.tick, g.i, PURPOSE_AGENT_TICK, w);
+        agent_tick_units(w, u);
+    }
+    spread_u = u[4];
+    if (pol == POL_RANDOM) {
+        if (CONT) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { a[c] = 2 * u[1 + c] - 1; raw[c] = (float)a[c]; }
+            adisc = 0;
+        } else {
+            adisc = (int)(w[0] >> 30);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) raw[c] = c == adisc ? 1.0f : 0.0f;
+        }
+    } else if (pol == POL_INSTINCT || pol == POL_INSTINCT_FF) {
+        instinct<N, CONT>(p, o, u[0], u[1], u[2], u[3], adisc, a);
+        if (CONT) {
+            if (pol == POL_INSTINCT_FF) a[2] = 1.0;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) raw[c] = (float)a[c];
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) raw[c] = c == adisc ? 1.0f : 0.0f;
+        }
+    }
+}
+
+template <int N, bool CONT>
+__global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
+    constexpr int P = 2 * N, L = 3 * N + 2;
+    Geo<N> g(global_warp(), p.E);
+    Lane<N> s;
+    double ret0, ret1;
+    load_lane(p, g, s, ret0, ret1);
+
+    float o[L];
+    const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT;  // kernel-uniform
+    if (need_obs) { gather(g, s); observe<N>(p, s, o); }
+    else {
+#pragma unroll
+        for (int c = 0; c < L; ++c) o[c] = -1.0f;
+    }
+
+    int adisc = 0;
+    double a[3] = {0, 0, 0}, spread_u = 0;
+    float raw[4];
+    const int pol = sa.pol[g.team];
+    if (g.valid) {
+        const double *drow = sa.draws ? sa.draws + (g.e * P + g.i) * 5 : nullptr;
+        if (pol == POL_EXTERNAL && sa.dtype != ACT_NONE) {
+            const long long idx = g.e * sa.act_agents + (sa.act_agents == P ? g.i : g.k);
+            if (!CONT) {
+                adisc = sa.dtype == ACT_I32 ? ((const int32_t *)sa.actions)[idx]
+                                            : argmax4((const float *)sa.actions + idx * 4);
+            } else if (sa.dtype == ACT_F32) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) a[c] = clip1((double)((const float *)sa.actions)[idx * 3 + c]);
+            } else {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) a[c] = clip1(((const double *)sa.actions)[idx * 3 + c]);
+            }
+            if (drow) spread_u = drow[4];
+            else {
+                uint32_t w[4]; double u[5];
+                env_philox(p, g.e, s.episode, s.tick, g.i, PURPOSE_AGENT_TICK, w);
+                agent_tick_units(w, u);
+                spread_u = u[4];
+            }
+        } else if (pol != POL_EXTERNAL) {
+            lane_policy<N, CONT>(p, g, s, pol, o, drow, adisc, a, spread_u, raw);
+        }
+    }
+
+    double rew;
+    Tally tl;
+    tick<N, CONT>(p, g, s, adisc, a, spread_u, rew, ret0, ret1, tl, sa.dtype == ACT_NONE);
+    if (sa.obs != nullptr) {
+        observe<N>(p, s, o);
+        if (g.valid) {
+            float *dst = sa.obs + (g.e * P + g.i) * L;
+#pragma unroll
+            for (int c = 0; c < L; ++c) dst[c] = o[c];
+        }
+    }
+    if (g.valid) {
+        const long long ai = g.e * P + g.i;
+        if (sa.rew) sa.rew[ai] = (float)rew;
+        if (sa.done) sa.done[ai] = (uint8_t)(s.env_done || s.hp <= 0);  // self.dones, battle_env.py:275,360,478,494
+        if (g.i == 0) {
+            if (sa.env_done) sa.env_done[g.e] = (uint8_t)s.env_done;
+            if (sa.winner) sa.winner[g.e] = (int8_t)s.winner;
+        }
+    }
+    store_lane(p, g, s, ret0, ret1, false);
+    flush_tally<N>(p, tl);
+}
+
+struct RolloutArgs {
+    int T, learner;
+    int pol[2];
+    const float *ext;     // [T,E,N,A] learner actions when pol[learner] == POL_EXTERNAL
+    bs_replay rp;
+    long long cursor_mod; // cursor % capacity
+    long long e_mod;      // E % capacity
+};
+
+template <int N, bool CONT>
+__global__ void __launch_bounds__(BLOCK) rollout_kernel(Params p, RolloutArgs ra) {
+    constexpr int L = 3 * N + 2, A = CONT ? 3 : 4;
+    Geo<N> g(global_warp(), p.E);
+    Lane<N> s;
+    double ret0, ret1;
+    load_lane(p, g, s, ret0, ret1);
+    gather(g, s);
+    float o[L];
+    observe<N>(p, s, o);
+    Tally tl;
+    const int pol = ra.pol[g.team];
+    const bool writer = g.valid && g.team == ra.learner && ra.rp.capacity > 0;
+    long long row = 0;
+    if (ra.rp.capacity > 0) row = (ra.cursor_mod + g.e % ra.rp.capacity) % ra.rp.capacity;
+
+    for (int t = 0; t < ra.T; ++t) {
+        // auto-reset: the game loop's env.reset() -- main.py:148
+        const bool need = g.valid && s.env_done;
+        if (__any_sync(FULL, need)) {
+            if (need) { reset_lane(p, g, s, false, nullptr); ret0 = ret1 = 0; }
+            gather(g, s);
+            float o2[L];
+            observe<N>(p, s, o2);
+            if (need) {
+#pragma unroll
+                for (int c = 0; c < L; ++c) o[c] = o2[c];
+            }
+        }
+        if (writer && ra.rp.state) {
+            float *dst = ra.rp.state + (row * N + g.k) * L;
+#pragma unroll
+            for (int c = 0; c < L; ++c) dst[c] = o[c];
+        }
+        int adisc = 0;
+        double a[3] = {0, 0, 0}, spread_u = 0;
+        float raw[4] = {0, 0, 0, 0};
+        if (g.valid) {
+            if (pol == POL_EXTERNAL) {
+                const float *src = ra.ext + (((long long)t * p.E + g.e) * N + g.k) * A;
+                if (CONT) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) { a[c] = clip1((double)src[c]); raw[c] = (float)a[c]; }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) raw[c] = src[c];
+                    adisc = argmax4(raw);
+                }
+                uint32_t w[4]; double u[5];
+                env_philox(p, g.e, s.episode, s.tick, g.i, PURPOSE_AGENT_TICK, w);
+                agent_tick_units(w, u);
+                spread_u = u[4];
+            } else {
+                lane_policy<N, CONT>(p, g, s, pol, o, nullptr, adisc, a, spread_u, raw);
+            }
+        }
+        double rew;
+        tick<N, CONT>(p, g, s, adisc, a, spread_u, rew, ret0, ret1, tl);
+        observe<N>(p, s, o);
+        if (writer) {
+            const long long ra_i = row * N + g.k;
+            if (ra.rp.new_state) {
+                float *dst = ra.rp.new_state + ra_i * L;
+#pragma unroll
+                for (int c = 0; c < L; ++c) dst[c] = o[c];
+            }
+            if (ra.rp.action) {
+#pragma unroll
+                for (int c = 0; c < A; ++c) ra.rp.action[ra_i * A + c] = raw[c];
+            }
+            if (ra.rp.reward) ra.rp.reward[ra_i] = (float)rew;
+            if (ra.rp.done) ra.rp.done[ra_i] = (uint8_t)(s.env_done || s.hp <= 0);
+        }
+        row += ra.e_mod;
+        if (row >= ra.rp.capacity) row -= ra.rp.capacity;
+    }
+    store_lane(p, g, s, ret0, ret1, true);
+    flush_tally<N>(p, tl);
+}
+
+template <int N, bool CONT>
+__global__ void __launch_bounds__(BLOCK) instinct_kernel(Params p, int team, const float *obs, const double *draws,
+                                                         void *out) {
+    constexpr int P = 2 * N, L = 3 * N + 2;
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= p.E * N) return;
+    const long long e = t / N;
+    const int k = (int)(t - e * N), i = team * N + k;
+    float o[L];
+    const float *src = obs + (e * P + i) * L;
+#pragma unroll
+    for (int c = 0; c < L; ++c) o[c] = src[c];
+    double u[5];
+    if (draws) {
+#pragma unroll
+        for (int c = 0; c < 5; ++c) u[c] = draws[(e * P + i) * 5 + c];
+    } else {
+        uint32_t w[4];
+        const uint32_t m = p.meta[e];
+        env_philox(p, e, p.episode[e], (int)(m & 0xffff), i, PURPOSE_AGENT_TICK, w);
+        agent_tick_units(w, u);
+    }
+    int adisc; double a[3];
+    instinct<N, CONT>(p, o, u[0], u[1], u[2], u[3], adisc, a);
+    if (CONT) {
+        double *dst = (double *)out + t * 3;
+        dst[0] = a[0]; dst[1] = a[1]; dst[2] = a[2];
+    } else {
+        ((int32_t *)out)[t] = adisc;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side: handle + C ABI
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(BS_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));            \
+    } while (0)
+
+struct bs_handle {
+    bs_config cfg;
+    int N, P, L, A;
+    bool cont;
+    int64_t E;
+    int device;
+    Params p;
+    std::vector<void *> allocs;
+    cudaStream_t hstream = nullptr;  // used by the *_host entry points
+    // device staging for *_host calls (grown on demand)
+    void *stage[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t stage_sz[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+};
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+template <typename T>
+static int dalloc(bs_handle *h, T **ptr, size_t n) {
+    void *q = nullptr;
+    CU(cudaMalloc(&q, n * sizeof(T)));
+    CU(cudaMemset(q, 0, n * sizeof(T)));
+    h->allocs.push_back(q);
+    *ptr = (T *)q;
+    return BS_OK;
+}
+
+static int stage_buf(bs_handle *h, int slot, size_t bytes, void **out) {
+    if (h->stage_sz[slot] < bytes) {
+        if (h->stage[slot]) CU(cudaFree(h->stage[slot]));
+        h->stage[slot] = nullptr; h->stage_sz[slot] = 0;
+        CU(cudaMalloc(&h->stage[slot], bytes));
+        h->stage_sz[slot] = bytes;
+    }
+    *out = h->stage[slot];
+    return BS_OK;
+}
+
+static int tie_tick_for(int n_agents) {  // battle_env.py:316-319: total_time accumulates 0.1 in double
+    volatile double t = 0;
+    int k = 0;
+    for (;;) { ++k; t = t + 0.1; if (t >= 10 + 2 * n_agents) return k; }
+}
+
+static inline int grid_for_envs(int64_t E, int N) {
+    const int K = 32 / (2 * N);
+    const int64_t warps = (E + K - 1) / K;
+    return (int)((warps * 32 + BLOCK - 1) / BLOCK);
+}
+
+#define DISPATCH_N(n_, ...)                                                  \
+    switch (n_) {                                                            \
+        case 1: { constexpr int N_ = 1; __VA_ARGS__; } break;                \
+        case 2: { constexpr int N_ = 2; __VA_ARGS__; } break;                \
+        case 3: { constexpr int N_ = 3; __VA_ARGS__; } break;                \
+        case 4: { constexpr int N_ = 4; __VA_ARGS__; } break;                \
+        case 5: { constexpr int N_ = 5; __VA_ARGS__; } break;                \
+        case 6: { constexpr int N_ = 6; __VA_ARGS__; } break;                \
+        case 7: { constexpr int N_ = 7; __VA_ARGS__; } break;                \
+        case 8: { constexpr int N_ = 8; __VA_ARGS__; } break;                \
+        default: return fail(BS_E_INVALID, "n_agents out of range");         \
+    }
+
+extern "C" {
+
+int bs_version(void) { return BS_VERSION; }
+const char *bs_last_error(void) { return g_err.c_str(); }
+
+int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int device, uint64_t seed, bs_handle **out) {
+    if (!cfg || !out) return fail(BS_E_INVALID, "null argument");
+    if (cfg->n_agents < 1 || cfg->n_agents > BS_MAX_AGENTS) return fail(BS_E_INVALID, "n_agents must be in 1..8");
+    if (n_envs < 1 || env_offset < 0) return fail(BS_E_INVALID, "n_envs must be >= 1 and env_offset >= 0");
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(BS_E_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(ce) + " (this library has no CPU path)");
+    if (device < 0 || device >= ndev) return fail(BS_E_INVALID, "bad device index");
+    DeviceGuard guard(device);
+    bs_handle *h = new (std::nothrow) bs_handle();
+    if (!h) return fail(BS_E_INVALID, "out of host memory");
+    h->cfg = *cfg; h->N = cfg->n_agents; h->P = 2 * h->N; h->L = 3 * h->N + 2;
+    h->cont = cfg->continuous_actions != 0; h->A = h->cont ? 3 : 4;
+    h->E = n_envs; h->device = device;
+    Params &p = h->p;
+    p.E = n_envs; p.env_offset = env_offset;
+    p.seed_lo = (uint32_t)seed; p.seed_hi = (uint32_t)(seed >> 32);
+    p.tie_tick = tie_tick_for(h->N);
+    p.r_hit_base = cfg->hit_base_reward; p.r_hit_plane = cfg->hit_plane_reward;
+    p.r_miss = cfg->miss_punishment; p.r_die = cfg->die_punishment; p.r_lose = cfg->lose_punishment;
+    p.diag = std::sqrt(std::pow(1200.0, 2) + std::pow(800.0, 2));
+    const size_t EP = (size_t)n_envs * h->P;
+    int rc;
+    if ((rc = dalloc(h, &p.plane_pos, EP)) || (rc = dalloc(h, &p.plane_dir, EP)) || (rc = dalloc(h, &p.plane_hp, EP)) ||
+        (rc = dalloc(h, &p.base_pos, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.base_hp, (size_t)n_envs * 2)) ||
+        (rc = dalloc(h, &p.bul_pos, EP * SLOTS)) || (rc = dalloc(h, &p.bul_vel, EP * SLOTS)) ||
+        (rc = dalloc(h, &p.meta, (size_t)n_envs)) || (rc = dalloc(h, &p.episode, (size_t)n_envs)) ||
+        (rc = dalloc(h, &p.ret, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.counters, 8))) {
+        bs_destroy(h);
+        return rc;
+    }
+    // every env starts "done" (nothing spawned yet): the first reset / rollout tick spawns it
+    std::vector<uint32_t> meta((size_t)n_envs, 1u << 16);
+    CU(cudaMemcpy(p.meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    CU(cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking));
+    *out = h;
+    return BS_OK;
+}
+
+int bs_destroy(bs_handle *h) {
+    if (!h) return BS_OK;
+    DeviceGuard guard(h->device);
+    cudaDeviceSynchronize();
+    for (void *q : h->allocs) cudaFree(q);
+    for (void *q : h->stage) if (q) cudaFree(q);
+    if (h->hstream) cudaStreamDestroy(h->hstream);
+    delete h;
+    return BS_OK;
+}
+
+int bs_reset(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float *obs, void *stream) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    DeviceGuard guard(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = grid_for_envs(h->E, h->N);
+    DISPATCH_N(h->N, reset_kernel<N_><<<grid, BLOCK, 0, st>>>(h->p, env_mask, draws, obs));
+    CU(cudaGetLastError());
+    return BS_OK;
+}
+
+static int launch_step(bs_handle *h, const StepArgs &sa, cudaStream_t st) {
+    const int grid = grid_for_envs(h->E, h->N);
+    if (h->cont) { DISPATCH_N(h->N, step_kernel<N_, true><<<grid, BLOCK, 0, st>>>(h->p, sa)); }
+    else { DISPATCH_N(h->N, step_kernel<N_, false><<<grid, BLOCK, 0, st>>>(h->p, sa)); }
+    CU(cudaGetLastError());
+    return BS_OK;
+}
+
+static int check_dtype(const bs_handle *h, int dt) {
+    if (h->cont) { if (dt != BS_ACT_F32 && dt != BS_ACT_F64) return fail(BS_E_INVALID, "continuous env takes BS_ACT_F32 or BS_ACT_F64 actions"); }
+    else if (dt != BS_ACT_I32 && dt != BS_ACT_F32) return fail(BS_E_INVALID, "discrete env takes BS_ACT_I32 or BS_ACT_F32 (logits) actions");
+    return BS_OK;
+}
+
+int bs_step(bs_handle *h, const void *actions, int action_dtype, const double *draws, float *obs, float *rew,
+            uint8_t *done, uint8_t *env_done, int8_t *winner, void *stream) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    if (action_dtype != BS_ACT_NONE) {
+        if (!actions) return fail(BS_E_INVALID, "null actions");
+        int rc = check_dtype(h, action_dtype); if (rc) return rc;
+    }
+    DeviceGuard guard(h->device);
+    StepArgs sa{actions, action_dtype, h->P, 0, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner};
+    return launch_step(h, sa, (cudaStream_t)stream);
+}
+
+int bs_step_team(bs_handle *h, int learner_team, const void *team_actions, int action_dtype, int other_policy,
+                 const double *draws, float *obs, float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner,
+                 void *stream) {
+    if (!h || !team_actions) return fail(BS_E_INVALID, "null handle or actions");
+    if (learner_team != 0 && learner_team != 1) return fail(BS_E_INVALID, "learner_team must be 0 (red) or 1 (blue)");
+    if (other_policy < BS_POL_RANDOM || other_policy > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "other_policy must be an in-kernel policy");
+    int rc = check_dtype(h, action_dtype); if (rc) return rc;
+    DeviceGuard guard(h->device);
+    StepArgs sa{team_actions, action_dtype, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner};
+    sa.pol[1 - learner_team] = other_policy;
+    return launch_step(h, sa, (cudaStream_t)stream);
+}
+
+int bs_instinct_actions(bs_handle *h, int team, const float *obs, const double *draws, void *actions_out, void *stream) {
+    if (!h || !obs || !actions_out) return fail(BS_E_INVALID, "null argument");
+    if (team != 0 && team != 1) return fail(BS_E_INVALID, "team must be 0 (red) or 1 (blue)");
+    DeviceGuard guard(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n = h->E * h->N;
+    const int grid = (int)((n + BLOCK - 1) / BLOCK);
+    if (h->cont) { DISPATCH_N(h->N, instinct_kernel<N_, true><<<grid, BLOCK, 0, st>>>(h->p, team, obs, draws, actions_out)); }
+    else { DISPATCH_N(h->N, instinct_kernel<N_, false><<<grid, BLOCK, 0, st>>>(h->p, team, obs, draws, actions_out)); }
+    CU(cudaGetLastError());
+    return BS_OK;
+}
+
+int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue, const float *ext_actions,
+                     const bs_replay *replay, int64_t cursor, void *stream) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    if (T < 1) return fail(BS_E_INVALID, "T must be >= 1");
+    if (learner_team != 0 && learner_team != 1) return fail(BS_E_INVALID, "learner_team must be 0 (red) or 1 (blue)");
+    const int pol[2] = {policy_red, policy_blue};
+    for (int t = 0; t < 2; ++t) {
+        if (pol[t] < BS_POL_EXTERNAL || pol[t] > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "unknown policy");
+        if (pol[t] == BS_POL_EXTERNAL && (t != learner_team || !ext_actions))
+            return fail(BS_E_INVALID, "BS_POL_EXTERNAL needs ext_actions and is only valid for learner_team");
+    }
+    if (cursor < 0) return fail(BS_E_INVALID, "cursor must be >= 0");
+    DeviceGuard guard(h->device);
+    RolloutArgs ra{};
+    ra.T = T; ra.learner = learner_team; ra.pol[0] = policy_red; ra.pol[1] = policy_blue; ra.ext = ext_actions;
+    if (replay && replay->capacity > 0) {
+        ra.rp = *replay;
+        ra.cursor_mod = cursor % replay->capacity;
+        ra.e_mod = h->E % replay->capacity;
+    } else {
+        std::memset(&ra.rp, 0, sizeof(ra.rp));
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = grid_for_envs(h->E, h->N);
+    if (h->cont) { DISPATCH_N(h->N, rollout_kernel<N_, true><<<grid, BLOCK, 0, st>>>(h->p, ra)); }
+    else { DISPATCH_N(h->N, rollout_kernel<N_, false><<<grid, BLOCK, 0, st>>>(h->p, ra)); }
+    CU(cudaGetLastError());
+    return BS_OK;
+}
+
+int bs_stats(bs_handle *h, int64_t out[8], void *stream) {
+    if (!h || !out) return fail(BS_E_INVALID, "null argument");
+    DeviceGuard guard(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaMemcpyAsync(out, h->p.counters, 8 * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return BS_OK;
+}
+
+int bs_stats_device(bs_handle *h, int64_t **dev_counters) {
+    if (!h || !dev_counters) return fail(BS_E_INVALID, "null argument");
+    *dev_counters = (int64_t *)h->p.counters;
+    return BS_OK;
+}
+
+// ---- state export / import (host views; checkpoint + parity injection) ---------------------------
+int bs_get_state(bs_handle *h, const bs_state_view *v) {
+    if (!h || !v) return fail(BS_E_INVALID, "null argument");
+    DeviceGuard guard(h->device);
+    CU(cudaDeviceSynchronize());
+    const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
+    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), epi((size_t)E), bp(EP * SLOTS), bv(EP * SLOTS);
+    std::vector<double> dir(EP), ret((size_t)E * 2);
+    std::vector<int8_t> hp(EP);
+    std::vector<int16_t> bhp((size_t)E * 2);
+    const Params &p = h->p;
+    CU(cudaMemcpy(pos.data(), p.plane_pos, EP * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(dir.data(), p.plane_dir, EP * 8, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(hp.data(), p.plane_hp, EP, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(bpos.data(), p.base_pos, (size_t)E * 8, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(bhp.data(), p.base_hp, (size_t)E * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(bp.data(), p.bul_pos, EP * SLOTS * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(bv.data(), p.bul_vel, EP * SLOTS * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(meta.data(), p.meta, (size_t)E * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(epi.data(), p.episode, (size_t)E * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(ret.data(), p.ret, (size_t)E * 16, cudaMemcpyDeviceToHost));
+    for (size_t a = 0; a < EP; ++a) {
+        if (v->plane_x) v->plane_x[a] = (int16_t)(pos[a] & 0xffff);
+        if (v->plane_y) v->plane_y[a] = (int16_t)(pos[a] >> 16);
+        if (v->plane_dir) v->plane_dir[a] = dir[a];
+        if (v->plane_hp) v->plane_hp[a] = hp[a];
+        for (int q = 0; q < SLOTS; ++q) {
+            const uint32_t vel = bv[(size_t)q * EP + a], ps = bp[(size_t)q * EP + a];
+            const bool valid = (vel & BV_VALID) != 0;
+            if (v->bullet_pos) {
+                v->bullet_pos[(a * SLOTS + q) * 2] = valid ? (int16_t)(ps & 0xffff) : (int16_t)-1;
+                v->bullet_pos[(a * SLOTS + q) * 2 + 1] = valid ? (int16_t)(ps >> 16) : (int16_t)-1;
+            }
+            if (v->bullet_vel) {
+                v->bullet_vel[(a * SLOTS + q) * 3] = (int8_t)(vel & 0xff);
+                v->bullet_vel[(a * SLOTS + q) * 3 + 1] = (int8_t)((vel >> 8) & 0xff);
+                v->bullet_vel[(a * SLOTS + q) * 3 + 2] = (int8_t)((vel >> 16) & 0xff);
+            }
+        }
+    }
+    for (int64_t e = 0; e < E; ++e) {
+        for (int t = 0; t < 2; ++t) {
+            if (v->base_pos) { v->base_pos[(e * 2 + t) * 2] = (int16_t)(bpos[e * 2 + t] & 0xffff); v->base_pos[(e * 2 + t) * 2 + 1] = (int16_t)(bpos[e * 2 + t] >> 16); }
+            if (v->base_hp) v->base_hp[e * 2 + t] = bhp[e * 2 + t];
+            if (v->team_return) v->team_return[e * 2 + t] = ret[e * 2 + t];
+        }
+        if (v->tick) v->tick[e] = (int32_t)(meta[e] & 0xffff);
+        if (v->env_done) v->env_done[e] = (uint8_t)((meta[e] >> 16) & 0xff);
+        if (v->winner) v->winner[e] = (int8_t)((meta[e] >> 24) & 0xff);
+        if (v->episode) v->episode[e] = epi[e];
+    }
+    return BS_OK;
+}
+
+int bs_set_state(bs_handle *h, const bs_state_view *v) {
+    if (!h || !v) return fail(BS_E_INVALID, "null argument");
+    if (!v->plane_x || !v->plane_y || !v->plane_dir || !v->plane_hp || !v->base_pos || !v->base_hp || !v->bullet_pos ||
+        !v->bullet_vel || !v->tick || !v->env_done || !v->winner || !v->episode || !v->team_return)
+        return fail(BS_E_INVALID, "bs_set_state needs every field of the view");
+    DeviceGuard guard(h->device);
+    CU(cudaDeviceSynchronize());
+    const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
+    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), bp(EP * SLOTS), bv(EP * SLOTS);
+    std::vector<int8_t> hp(EP);
+    for (size_t a = 0; a < EP; ++a) {
+        pos[a] = (uint32_t)(uint16_t)v->plane_x[a] | ((uint32_t)(uint16_t)v->plane_y[a] << 16);
+        for (int q = 0; q < SLOTS; ++q) {
+            const int8_t *vel = v->bullet_vel + (a * SLOTS + q) * 3;
+            const int16_t *ps = v->bullet_pos + (a * SLOTS + q) * 2;
+            const uint32_t w = (uint32_t)(uint8_t)vel[0] | ((uint32_t)(uint8_t)vel[1] << 8) | ((uint32_t)(uint8_t)vel[2] << 16);
+            const bool valid = (w & BV_VALID) != 0 && q < SLOTS - 1;
+            bv[(size_t)q * EP + a] = valid ? w : 0u;
+            bp[(size_t)q * EP + a] = valid ? ((uint32_t)(uint16_t)ps[0] | ((uint32_t)(uint16_t)ps[1] << 16)) : 0u;
+        }
+    }
+    for (int64_t e = 0; e < E; ++e) {
+        for (int t = 0; t < 2; ++t)
+            bpos[e * 2 + t] = (uint32_t)(uint16_t)v->base_pos[(e * 2 + t) * 2] | ((uint32_t)(uint16_t)v->base_pos[(e * 2 + t) * 2 + 1] << 16);
+        meta[e] = ((uint32_t)v->tick[e] & 0xffff) | ((uint32_t)(v->env_done[e] ? 1 : 0) << 16) | ((uint32_t)(uint8_t)v->winner[e] << 24);
+    }
+    const Params &p = h->p;
+    CU(cudaMemcpy(p.plane_pos, pos.data(), EP * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.plane_dir, v->plane_dir, EP * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.plane_hp, v->plane_hp, EP, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.base_pos, bpos.data(), (size_t)E * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.base_hp, v->base_hp, (size_t)E * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.bul_pos, bp.data(), EP * SLOTS * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.bul_vel, bv.data(), EP * SLOTS * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.meta, meta.data(), (size_t)E * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.episode, v->episode, (size_t)E * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.ret, v->team_return, (size_t)E * 16, cudaMemcpyHostToDevice));
+    return BS_OK;
+}
+
+// ---- host-buffer entry points ---------------------------------------------------------------------
+static size_t action_bytes(const bs_handle *h, int dtype, int agents) {
+    const size_t n = (size_t)h->E * agents;
+    if (dtype == BS_ACT_I32) return n * 4;
+    if (dtype == BS_ACT_F32) return n * h->A * 4;
+    return n * 3 * 8;
+}
+
+#define H2D(slot, host, bytes, devptr)                                                     \
+    do {                                                                                   \
+        void *d_ = nullptr;                                                                \
+        if (host) {                                                                        \
+            int rc_ = stage_buf(h, slot, bytes, &d_); if (rc_) return rc_;                 \
+            CU(cudaMemcpyAsync(d_, host, bytes, cudaMemcpyHostToDevice, h->hstream));      \
+        }                                                                                  \
+        devptr = decltype(devptr)(d_);                                                     \
+    } while (0)
+#define DOUT(slot, host, bytes, devptr)                                                    \
+    do {                                                                                   \
+        void *d_ = nullptr;                                                                \
+        if (host) { int rc_ = stage_buf(h, slot, bytes, &d_); if (rc_) return rc_; }       \
+        devptr = decltype(devptr)(d_);                                                     \
+    } while (0)
+#define D2H(host, devptr, bytes)                                                           \
+    do { if (host) CU(cudaMemcpyAsync(host, devptr, bytes, cudaMemcpyDeviceToHost, h->hstream)); } while (0)
+
+int bs_reset_host(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float *obs) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    DeviceGuard guard(h->device);
+    const uint8_t *d_mask; const int32_t *d_draws; float *d_obs;
+    H2D(0, env_mask, (size_t)h->E, d_mask);
+    H2D(1, draws, (size_t)h->E * (4 + 6 * h->N) * 4, d_draws);
+    DOUT(2, obs, (size_t)h->E * h->P * h->L * 4, d_obs);
+    int rc = bs_reset(h, d_mask, d_draws, d_obs, h->hstream); if (rc) return rc;
+    D2H(obs, d_obs, (size_t)h->E * h->P * h->L * 4);
+    CU(cudaStreamSynchronize(h->hstream));
+    return BS_OK;
+}
+
+static int step_host_common(bs_handle *h, bool team_mode, int learner_team, const void *actions, int action_dtype,
+                            int other_policy, const double *draws, float *obs, float *rew, uint8_t *done,
+                            uint8_t *env_done, int8_t *winner) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    int rc;
+    if (action_dtype == BS_ACT_NONE && !team_mode) actions = nullptr;
+    else {
+        if (!actions) return fail(BS_E_INVALID, "null actions");
+        rc = check_dtype(h, action_dtype); if (rc) return rc;
+    }
+    DeviceGuard guard(h->device);
+    const size_t EP = (size_t)h->E * h->P;
+    const void *d_act; const double *d_draws; float *d_obs, *d_rew; uint8_t *d_done, *d_edone; int8_t *d_win;
+    H2D(0, actions, action_bytes(h, action_dtype, team_mode ? h->N : h->P), d_act);
+    H2D(1, draws, EP * 5 * 8, d_draws);
+    DOUT(2, obs, EP * h->L * 4, d_obs);
+    DOUT(3, rew, EP * 4, d_rew);
+    DOUT(4, done, EP, d_done);
+    DOUT(5, env_done, (size_t)h->E, d_edone);
+    DOUT(6, winner, (size_t)h->E, d_win);
+    rc = team_mode ? bs_step_team(h, learner_team, d_act, action_dtype, other_policy, d_draws, d_obs, d_rew, d_done, d_edone, d_win, h->hstream)
+                   : bs_step(h, d_act, action_dtype, d_draws, d_obs, d_rew, d_done, d_edone, d_win, h->hstream);
+    if (rc) return rc;
+    D2H(obs, d_obs, EP * h->L * 4);
+    D2H(rew, d_rew, EP * 4);
+    D2H(done, d_done, EP);
+    D2H(env_done, d_edone, (size_t)h->E);
+    D2H(winner, d_win, (size_t)h->E);
+    CU(cudaStreamSynchronize(h->hstream));
+    return BS_OK;
+}
+
+int bs_step_host(bs_handle *h, const void *actions, int action_dtype, const double *draws, float *obs, float *rew,
+                 uint8_t *done, uint8_t *env_done, int8_t *winner) {
+    return step_host_common(h, false, 0, actions, action_dtype, 0, draws, obs, rew, done, env_done, winner);
+}
+
+int bs_step_team_host(bs_handle *h, int learner_team, const void *team_actions, int action_dtype, int other_policy,
+                      const double *draws, float *obs, float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner) {
+    return step_host_common(h, true, learner_team, team_actions, action_dtype, other_policy, draws, obs, rew, done, env_done, winner);
+}
+
+int bs_instinct_actions_host(bs_handle *h, int team, const float *obs, const double *draws, void *actions_out) {
+    if (!h || !obs || !actions_out) return fail(BS_E_INVALID, "null argument");
+    DeviceGuard guard(h->device);
+    const size_t EP = (size_t)h->E * h->P;
+    const size_t out_bytes = (size_t)h->E * h->N * (h->cont ? 24 : 4);
+    const float *d_obs; const double *d_draws; void *d_out;
+    H2D(2, obs, EP * h->L * 4, d_obs);
+    H2D(1, draws, EP * 5 * 8, d_draws);
+    DOUT(7, actions_out, out_bytes, d_out);
+    int rc = bs_instinct_actions(h, team, d_obs, d_draws, d_out, h->hstream); if (rc) return rc;
+    D2H(actions_out, d_out, out_bytes);
+    CU(cudaStreamSynchronize(h->hstream));
+    return BS_OK;
+}
+
+int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
+                          const float *ext_actions, const bs_replay *replay, int64_t cursor, int64_t stats_out[8]) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    if (T < 1) return fail(BS_E_INVALID, "T must be >= 1");
+    DeviceGuard guard(h->device);
+    const float *d_ext;
+    H2D(8, ext_actions, (size_t)T * h->E * h->N * h->A * 4, d_ext);
+    int rc = bs_rollout_fused(h, T, learner_team, policy_red, policy_blue, d_ext, replay, cursor, h->hstream);
+    if (rc) return rc;
+    if (stats_out) CU(cudaMemcpyAsync(stats_out, h->p.counters, 8 * sizeof(int64_t), cudaMemcpyDeviceToHost, h->hstream));
+    CU(cudaStreamSynchronize(h->hstream));
+    return BS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,492 @@
+// tick.cuh -- device-side Battlespace tick for sm_100a.
+//
+// Mapping: one LANE per plane, one env per group of G = 2N consecutive lanes (red planes first),
+// K = 32 / G envs per warp.  Everything an env needs lives in the registers of its G lanes:
+// the lane's own plane, its own 12 bullet slots (an age-indexed shift register), and replicated
+// copies of the enemy planes / bases kept consistent with warp shuffles.  Control flow that
+// contains a shuffle is warp-uniform; per-env conditions are predicates.
+//
+// Arithmetic follows the reference operation by operation in IEEE double (compiled with
+// --fmad=false so that no multiply-add is contracted), see the citations on each function.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace bs {
+
+constexpr int SLOTS = 12;
+constexpr unsigned FULL = 0xffffffffu;
+constexpr double PI = 3.14159265358979323846;
+constexpr double DEG2RAD = PI / 180.0;  // math.radians
+constexpr double RAD2DEG = 180.0 / PI;  // math.degrees
+constexpr double TWO_PI = 2 * PI;
+
+// bullet velocity word: sx (int8) | sy (int8) << 8 | flags << 16
+constexpr uint32_t BV_VALID = 1u << 16, BV_XEXACT = 1u << 17, BV_YEXACT = 1u << 18;
+
+enum { W_NONE = 0, W_RED = 1, W_BLUE = 2, W_TIE = 3 };
+enum { POL_EXTERNAL = 0, POL_RANDOM = 1, POL_INSTINCT = 2, POL_INSTINCT_FF = 3 };
+enum { ACT_I32 = 0, ACT_F32 = 1, ACT_F64 = 2, ACT_NONE = 3 };
+enum { PURPOSE_AGENT_TICK = 0, PURPOSE_RESET_PLANE = 1, PURPOSE_RESET_BASE = 2 };
+enum { C_WINS_RED = 0, C_WINS_BLUE, C_TIES, C_GAMES, C_RET_RED, C_RET_BLUE, C_TICKS, C_AGENT_STEPS };
+
+struct Params {
+    long long E;          // envs in this handle
+    long long env_offset; // global index of env 0 (sharding)
+    uint32_t seed_lo, seed_hi;
+    int tie_tick;         // first step call whose accumulated 0.1s reach 10+2N (battle_env.py:316-319)
+    double r_hit_base, r_hit_plane, r_miss, r_die, r_lose;
+    double diag;          // sqrt(1200^2 + 800^2), battle_env.py:230
+    // SoA state (see DESIGN.md "Data layout in HBM")
+    uint32_t *plane_pos;  // [E*2N]      x | y<<16
+    double *plane_dir;    // [E*2N]
+    int8_t *plane_hp;     // [E*2N]
+    uint32_t *base_pos;   // [E*2]       x | y<<16
+    int16_t *base_hp;     // [E*2]
+    uint32_t *bul_pos;    // [12][E*2N]  x | y<<16 (slot-major: coalesced per slot)
+    uint32_t *bul_vel;    // [12][E*2N]
+    uint32_t *meta;       // [E]         tick | env_done<<16 | winner<<24
+    uint32_t *episode;    // [E]
+    double *ret;          // [E*2]
+    unsigned long long *counters;  // [8]
+};
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al. 2011); counter layout in include/battlespace.h
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                              uint32_t k0, uint32_t k1, uint32_t (&w)[4]) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+        uint32_t h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = h1 ^ c1 ^ k0, n2 = h0 ^ c3 ^ k1;
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    w[0] = c0; w[1] = c1; w[2] = c2; w[3] = c3;
+}
+
+__device__ __forceinline__ void env_philox(const Params &p, long long e, uint32_t episode, int tick,
+                                           int agent, int purpose, uint32_t (&w)[4]) {
+    unsigned long long g = (unsigned long long)(p.env_offset + e);
+    philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), episode,
+                  ((uint32_t)tick << 16) | ((uint32_t)agent << 8) | (uint32_t)purpose, p.seed_lo,
+                  p.seed_hi, w);
+}
+
+__device__ __forceinline__ int randint_from(uint32_t w, int lo, int hi) {
+    return lo + (int)__umulhi(w, (uint32_t)(hi - lo + 1));
+}
+
+// unit draws of an agent-tick block: u[0]=shoot_u, u[1..3]=noise_u, u[4]=spread_u
+__device__ __forceinline__ void agent_tick_units(const uint32_t (&w)[4], double (&u)[5]) {
+    u[1] = (double)(w[0] >> 8) * (1.0 / 16777216.0);
+    u[2] = (double)(w[1] >> 8) * (1.0 / 16777216.0);
+    u[3] = (double)(w[2] >> 8) * (1.0 / 16777216.0);
+    u[0] = (double)(((w[0] & 0xffu) << 16) | ((w[1] & 0xffu) << 8) | (w[2] & 0xffu)) * (1.0 / 16777216.0);
+    u[4] = (double)w[3] * (1.0 / 4294967296.0);
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int N>
+struct Geo {
+    static constexpr int P = 2 * N;       // planes per env
+    static constexpr int G = P;           // lanes per env
+    static constexpr int K = 32 / G;      // envs per warp
+    static constexpr int L = 3 * N + 2;   // observation length, battle_env.py:132
+    int lane, i, team, k;                 // lane in warp; agent index; team; index in team
+    int gb, tb, eb;                       // first lane of: my env, my team, the enemy team
+    unsigned gmask;                       // lanes of my env
+    bool valid;                           // lane maps to an env < E
+    long long e;                          // env index within the handle
+
+    __device__ __forceinline__ Geo(long long warp_id, long long E) {
+        lane = threadIdx.x & 31;
+        int sub = lane / G;
+        i = lane - sub * G;
+        team = i >= N;
+        k = i - team * N;
+        e = warp_id * K + sub;
+        valid = sub < K && e < E;
+        if (!valid) sub = 0;  // keep shuffle sources in range for idle lanes
+        gb = sub * G;
+        tb = gb + team * N;
+        eb = gb + (1 - team) * N;
+        gmask = (G == 32 ? FULL : ((1u << G) - 1u)) << gb;
+    }
+};
+
+// Registers of one lane.
+template <int N>
+struct Lane {
+    int x, y, hp;           // own plane: rect centre (sprites.py:84,131) and hit points
+    double dir;             // own direction in degrees (sprites.py:67,99)
+    uint32_t bp[SLOTS];     // own bullets, index = age before this tick's update
+    uint32_t bv[SLOTS];
+    int ebx, eby;           // enemy base centre
+    int bhp_own, bhp_enemy; // base hit points (replicated over the group)
+    int tick, env_done, winner;
+    uint32_t episode;
+    // replicated view of the enemy team, refreshed by gather()
+    int ex[N], ey[N], ehp[N];
+    unsigned am;            // bit j: enemy j is in self.agents (hp > 0)
+};
+
+template <int N>
+__device__ __forceinline__ void gather(const Geo<N> &g, Lane<N> &s) {
+    // x 11 bits | y 10 bits | hp 3 bits
+    uint32_t mine = (uint32_t)s.x | ((uint32_t)s.y << 11) | ((uint32_t)(s.hp > 0 ? s.hp : 0) << 21);
+    s.am = 0;
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+        uint32_t v = __shfl_sync(FULL, mine, g.eb + j);
+        s.ex[j] = v & 0x7ff; s.ey[j] = (v >> 11) & 0x3ff; s.ehp[j] = (v >> 21) & 7;
+        s.am |= (s.ehp[j] > 0 ? 1u : 0u) << j;
+    }
+}
+
+// rel_angle / 360 -- battle_env.py:38-52,231 ; dist / diag * 2 - 1 -- battle_env.py:54-58,230
+__device__ __forceinline__ void pair_obs(const Params &p, int x0, int y0, double a0, int x1, int y1,
+                                         float &od, float &oa) {
+    int dx = x0 - x1, dy = y0 - y1;
+    double d = sqrt((double)(dx * dx + dy * dy));
+    od = (float)(d / p.diag * 2 - 1);
+    double r = atan2((double)dy, (double)dx);
+    if (r < 0) r += TWO_PI;                    // Python float %: fmod plus sign fix-up
+    double degs = r * RAD2DEG;
+    double rel = 180 + a0 - (360 - degs);
+    if (rel < -180) rel += 360;
+    if (rel > 180) rel -= 360;
+    oa = (float)(rel / 360);
+}
+
+// observe -- battle_env.py:202-244, for the lane's own plane; needs a fresh gather().
+template <int N>
+__device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float (&o)[3 * N + 2]) {
+#pragma unroll
+    for (int c = 0; c < 3 * N + 2; ++c) o[c] = -1.0f;
+    if (s.hp > 0) {
+        pair_obs(p, s.x, s.y, s.dir, s.ebx, s.eby, o[0], o[1]);
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            if (s.ehp[j] > 0) {
+                o[2 + 3 * j] = 1.0f;
+                pair_obs(p, s.x, s.y, s.dir, s.ex[j], s.ey[j], o[3 + 3 * j], o[4 + 3 * j]);
+            }
+        }
+    }
+}
+
+// InstinctAgent.choose_action -- instinct/agent.py:10-62 (float32 obs decoded in double:
+// numpy 1.23.1 promotion).  Continuous: a[0..2]; discrete: adisc.
+template <int N, bool CONT>
+__device__ __forceinline__ void instinct(const Params &p, const float (&o)[3 * N + 2], double shoot_u,
+                                         double n0, double n1, double n2, int &adisc, double (&a)[3]) {
+    double td = ((double)o[0] + 1) / 2 * p.diag;
+    double ta = (double)o[1] * 360;
+    double best = td * fabs(ta);  // base wins ties: replaced only by a strictly smaller score
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+        double dj = ((double)o[3 + 3 * j] + 1) / 2 * p.diag;
+        double aj = (double)o[4 + 3 * j] * 360;
+        double sc = (o[2 + 3 * j] == 1.0f) ? dj * fabs(aj) : 1000000.0;
+        if (sc < best) { best = sc; td = dj; ta = aj; }
+    }
+    if (CONT) {
+        double a2 = 0;
+        if (td < 500.0 / 3 * 2 && fabs(ta) < 20) a2 = shoot_u < 0.6 ? 1.0 : -1.0;
+        double a0 = td / p.diag * 2 - 1;
+        double v = -ta / 35, a1;
+        if (ta > 0) a1 = v > -1 ? v : -1; else a1 = v < 1 ? v : 1;
+        double t0 = a0 + (-0.15 + (0.15 - -0.15) * n0);
+        double t1 = a1 + (-0.15 + (0.15 - -0.15) * n1);
+        double t2 = a2 + (-0.15 + (0.15 - -0.15) * n2);
+        a[0] = t0 < -1 ? -1 : (t0 > 1 ? 1 : t0);
+        a[1] = t1 < -1 ? -1 : (t1 > 1 ? 1 : t1);
+        a[2] = t2 < -1 ? -1 : (t2 > 1 ? 1 : t2);
+        adisc = 0;
+    } else {
+        adisc = (td < 500.0 / 2 && fabs(ta) < 20) ? 1 : (ta > 0 ? 3 : 2);
+        a[0] = a[1] = a[2] = 0;
+    }
+}
+
+// Plane.forward + clamp -- sprites.py:35-42,123-141 (rect.center = floats: C cast, then the
+// screen clamp; centre x in [25,1175], y in [24,776] for the 50x48 sprite)
+__device__ __forceinline__ void plane_forward(int &x, int &y, double dir, double speed) {
+    double rad = -(dir * DEG2RAD);
+    double sn, cs;
+    sincos(rad, &sn, &cs);
+    double st = speed * 0.1;
+    int nx = (int)((double)x + st * cs);
+    int ny = (int)((double)y + st * sn);
+    x = min(max(nx, 25), 1175);
+    y = min(max(ny, 24), 776);
+}
+
+// Plane.rotate -- sprites.py:93-103
+__device__ __forceinline__ double plane_rotate(double dir, double a) {
+    dir += a;
+    while (dir > 360) dir -= 360;
+    while (dir < 0) dir += 360;
+    return dir;
+}
+
+// Per-lane event counters accumulated over a launch (only the env's first lane counts).
+struct Tally {
+    int wins_red = 0, wins_blue = 0, ties = 0, games = 0, ticks = 0;
+    long long ret_red = 0, ret_blue = 0;
+};
+
+// One env tick -- parallel_env.step, battle_env.py:281-381.
+//   adisc / a[3] : this lane's decoded action (clipped / argmax-ed);  spread_u : its Bullet draw.
+//   rew          : this lane's reward for the tick (double, reference accumulation order).
+// On return s holds the new state and gather() data is current (positions after the move,
+// enemy hp after the bullet loop), so observe() can be called directly.
+template <int N, bool CONT>
+__device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &s, int adisc,
+                                     const double (&a)[3], double spread_u, double &rew,
+                                     double &ret0, double &ret1, Tally &tl, bool no_actions = false) {
+    rew = 0.0;
+    const bool active = g.valid && !s.env_done;                        // :303-306
+    const unsigned alive_b = __ballot_sync(FULL, active && s.hp > 0);
+    const bool any_alive = !no_actions && (alive_b & g.gmask) != 0;    // len(actions) == 0 also ties
+    const bool tie_now = active && !any_alive;                         // :309-313
+    const bool adv = active && any_alive;
+    s.tick += adv ? 1 : 0;                                             // :316
+    const bool time_tie = adv && s.tick >= p.tie_tick;                 // :319-323
+    const bool run = adv && !time_tie;
+
+    // ---- actions of the planes that are alive, :325-329 + process_action :383-424 -----------
+    const int x0 = s.x, y0 = s.y;
+    const double d0 = s.dir;
+    bool shoot = false;
+    if (run && s.hp > 0) {
+        if (CONT) {
+            double speed = ((a[0] + 1) / 2) * (275 - 200) + 200;
+            plane_forward(s.x, s.y, s.dir, speed);
+            s.dir = plane_rotate(s.dir, a[1] * 35);
+            shoot = a[2] > 0;
+        } else if (adisc >= 0 && adisc <= 3) {
+            shoot = adisc == 1;
+            if (adisc == 2) s.dir = plane_rotate(s.dir, 15);
+            if (adisc == 3) s.dir = plane_rotate(s.dir, -15);
+            plane_forward(s.x, s.y, s.dir, 215);
+        }
+    }
+    // Bullet.__init__ -- sprites.py:293-318.  From here on the bullet is integer: its per-update
+    // displacement d = 45*cos/sin is constant, and trunc(int + d) == int + floor(d) except that
+    // a result in (-1,0) truncates to 0 (flagged "exact" when d itself is an integer).
+    s.bv[0] = 0;
+    if (shoot) {
+        double bd = d0 + (spread_u * 8 - 4);
+        double rad = -(bd * DEG2RAD);
+        double sn, cs;
+        sincos(rad, &sn, &cs);
+        double ddx = (450 * 0.1) * cs, ddy = (450 * 0.1) * sn;
+        double fx = floor(ddx), fy = floor(ddy);
+        s.bp[0] = (uint32_t)x0 | ((uint32_t)y0 << 16);
+        s.bv[0] = ((uint32_t)(int)fx & 0xffu) | (((uint32_t)(int)fy & 0xffu) << 8) | BV_VALID |
+                  (fx == ddx ? BV_XEXACT : 0u) | (fy == ddy ? BV_YEXACT : 0u);
+    }
+
+    gather(g, s);  // enemy positions after the move, hp before the bullet loop
+
+    // ---- bullets, oldest first; same age: agent order -- :332-360, sprites.py:321-351 --------
+    int base_hits = 0;
+#pragma unroll
+    for (int q = SLOTS - 1; q >= 0; --q) {
+        const uint32_t v = s.bv[q];
+        const bool bvalid = run && (v & BV_VALID);
+        int bx = (int)(s.bp[q] & 0xffffu) + (int)(int8_t)(v & 0xffu);
+        int by = (int)(s.bp[q] >> 16) + (int)(int8_t)((v >> 8) & 0xffu);
+        if (bx == -1 && !(v & BV_XEXACT)) bx = 0;
+        if (by == -1 && !(v & BV_YEXACT)) by = 0;
+        const bool miss = (q == SLOTS - 1) || (unsigned)bx > 1200u || (unsigned)by > 800u;
+        // colliderect closed forms: base -34<dx<34, -33<dy<32; plane -28<dx<28, -26<dy<25
+        const bool bhit = !miss && (unsigned)(bx - s.ebx + 33) < 67u && (unsigned)(by - s.eby + 32) < 64u;
+        unsigned cm = 0;
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+            cm |= (((unsigned)(bx - s.ex[j] + 27) < 55u && (unsigned)(by - s.ey[j] + 25) < 50u) ? 1u : 0u) << j;
+        if (!(bvalid && !miss && !bhit)) cm = 0;
+        int cand = -1;
+        bool died_now = false;
+        if (__any_sync(FULL, (cm & s.am) != 0)) {
+            // Somebody in the warp hits a plane at this age.  Resolve the N same-age bullets of
+            // each team in agent order; a plane that dies is invisible to the later ones.
+#pragma unroll
+            for (int kk = 0; kk < N; ++kk) {
+                unsigned m = cm & s.am;
+                int c_me = m ? (__ffs(m) - 1) : -1;
+                int c_team = __shfl_sync(FULL, c_me, g.tb + kk);   // teammate kk's victim
+                int c_foe = __shfl_sync(FULL, c_me, g.eb + kk);    // enemy kk's victim
+                if (kk == g.k) cand = c_me;
+#pragma unroll
+                for (int j = 0; j < N; ++j)
+                    if (c_team == j) { s.ehp[j] -= 1; if (s.ehp[j] <= 0) s.am &= ~(1u << j); }
+                if (g.valid && c_foe == g.k && s.hp > 0) { s.hp -= 1; died_now = died_now || s.hp <= 0; }
+            }
+        }
+        const bool removed = bvalid && (miss || bhit || cand >= 0);
+        const double own = miss ? p.r_miss : (bhit ? p.r_hit_base : p.r_hit_plane);
+        base_hits += (bvalid && bhit) ? 1 : 0;
+        // reference order inside one age: red bullets first, so a blue victim's die_punishment
+        // precedes its own bullet's outcome and a red victim's follows it
+        if (died_now && g.team == 1) rew += p.r_die;
+        if (removed) rew += own;
+        if (died_now && g.team == 0) rew += p.r_die;
+        if (removed) s.bv[q] = 0;
+        else if (bvalid) s.bp[q] = (uint32_t)bx | ((uint32_t)by << 16);
+    }
+    // age the shift register
+    if (run) {
+#pragma unroll
+        for (int q = SLOTS - 1; q > 0; --q) { s.bp[q] = s.bp[q - 1]; s.bv[q] = s.bv[q - 1]; }
+        s.bv[0] = 0;
+    }
+    // base damage: no alive check, hp may go negative
+    int mine_total = 0, foe_total = 0;
+#pragma unroll
+    for (int kk = 0; kk < N; ++kk) {
+        mine_total += __shfl_sync(FULL, base_hits, g.tb + kk);
+        foe_total += __shfl_sync(FULL, base_hits, g.eb + kk);
+    }
+    s.bhp_enemy -= mine_total;
+    s.bhp_own -= foe_total;
+
+    // ---- win / tie -- :363-372, 469-496 -------------------------------------------------------
+    const bool i_won = run && s.bhp_enemy <= 0;  // the winners' planes get lose_punishment (sic)
+    const bool foe_won = run && s.bhp_own <= 0;
+    if (i_won) rew += p.r_lose;
+    const bool red_won = g.team == 0 ? i_won : foe_won, blue_won = g.team == 0 ? foe_won : i_won;
+    const bool tie = tie_now || time_tie;
+    if (red_won) s.winner = W_RED;
+    if (blue_won) s.winner = W_BLUE;  // both bases dead: ends as 'blue', two games counted
+    if (tie) s.winner = W_TIE;
+    if (red_won || blue_won || tie) s.env_done = 1;
+
+    // ---- report sums (main.py:193-203,218-253); the env's first lane keeps them ----------------
+    double r0 = 0, r1 = 0;
+#pragma unroll
+    for (int kk = 0; kk < N; ++kk) {
+        r0 += __shfl_sync(FULL, rew, g.gb + kk);
+        r1 += __shfl_sync(FULL, rew, g.gb + N + kk);
+    }
+    if (active && g.i == 0) {
+        ret0 += r0; ret1 += r1;
+        tl.ticks += 1;
+        tl.wins_red += red_won; tl.wins_blue += blue_won; tl.ties += tie;
+        tl.games += (int)red_won + (int)blue_won + (int)tie;
+        if (s.env_done) {
+            tl.ret_red += __double2ll_rn(ret0 * 1048576.0);
+            tl.ret_blue += __double2ll_rn(ret1 * 1048576.0);
+        }
+    }
+}
+
+// parallel_env.reset for one lane -- battle_env.py:246-279, sprites.py:74-91,238-252.
+// d_* are this lane's spawn values when injected (inj=true), else Philox.
+template <int N>
+__device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lane<N> &s, bool inj,
+                                           const int32_t *draws /* this env's [4+6N] or null */) {
+    s.episode += 1;
+    int rbx, rby, bbx, bby, px, py, pd;
+    if (inj) {
+        rbx = draws[0]; rby = draws[1]; bbx = draws[2]; bby = draws[3];
+        px = draws[4 + 3 * g.i]; py = draws[5 + 3 * g.i]; pd = draws[6 + 3 * g.i];
+    } else {
+        uint32_t w[4];
+        env_philox(p, g.e, s.episode, 0, 0, PURPOSE_RESET_BASE, w);
+        rbx = randint_from(w[0], 62, 379); rby = randint_from(w[1], 62, 738);       // sprites.py:246-247
+        bbx = randint_from(w[2], 758, 1138); bby = randint_from(w[3], 62, 738);     // sprites.py:250-251
+        env_philox(p, g.e, s.episode, 0, g.i, PURPOSE_RESET_PLANE, w);
+        if (g.team == 0) { px = randint_from(w[0], 50, 383); pd = randint_from(w[2], 270, 450); }  // :82-85
+        else { px = randint_from(w[0], 766, 1150); pd = randint_from(w[2], 90, 270); }             // :88-91
+        py = randint_from(w[1], 48, 752);
+    }
+    if (g.team == 0 && pd >= 360) pd -= 360;                                        // sprites.py:86
+    s.x = px; s.y = py; s.dir = (double)pd; s.hp = 4;                               // battle_env.py:92
+    s.ebx = g.team == 0 ? bbx : rbx; s.eby = g.team == 0 ? bby : rby;
+    s.bhp_own = s.bhp_enemy = 5 * N;                                                // battle_env.py:91
+#pragma unroll
+    for (int q = 0; q < SLOTS; ++q) { s.bp[q] = 0; s.bv[q] = 0; }
+    s.tick = 0; s.env_done = 0; s.winner = W_NONE;
+}
+
+// ---- state <-> registers ------------------------------------------------------------------------
+template <int N>
+__device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane<N> &s, double &ret0,
+                                          double &ret1) {
+    constexpr int P = 2 * N;
+    s.x = s.y = 0; s.hp = 0; s.dir = 0; s.ebx = s.eby = 0; s.bhp_own = s.bhp_enemy = 0;
+    s.tick = 0; s.env_done = 1; s.winner = 0; s.episode = 0; ret0 = ret1 = 0;
+#pragma unroll
+    for (int q = 0; q < SLOTS; ++q) { s.bp[q] = 0; s.bv[q] = 0; }
+    if (g.valid) {
+        const long long a = g.e * P + g.i, EP = p.E * P;
+        uint32_t pos = p.plane_pos[a];
+        s.x = pos & 0xffff; s.y = pos >> 16;
+        s.dir = p.plane_dir[a];
+        s.hp = p.plane_hp[a];
+        uint32_t eb = p.base_pos[g.e * 2 + (1 - g.team)];
+        s.ebx = eb & 0xffff; s.eby = eb >> 16;
+        s.bhp_own = p.base_hp[g.e * 2 + g.team];
+        s.bhp_enemy = p.base_hp[g.e * 2 + (1 - g.team)];
+        uint32_t m = p.meta[g.e];
+        s.tick = m & 0xffff; s.env_done = (m >> 16) & 0xff; s.winner = (m >> 24) & 0xff;
+        s.episode = p.episode[g.e];
+#pragma unroll
+        for (int q = 0; q < SLOTS - 1; ++q) {  // HBM slot q holds age q+1; ages 1..11 exist between ticks
+            s.bv[q + 1] = p.bul_vel[q * EP + a];
+            s.bp[q + 1] = p.bul_pos[q * EP + a];
+        }
+        if (g.i == 0) { ret0 = p.ret[g.e * 2]; ret1 = p.ret[g.e * 2 + 1]; }
+    }
+}
+
+template <int N>
+__device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, const Lane<N> &s,
+                                           double ret0, double ret1, bool base_pos_too) {
+    constexpr int P = 2 * N;
+    if (!g.valid) return;
+    const long long a = g.e * P + g.i, EP = p.E * P;
+    p.plane_pos[a] = (uint32_t)s.x | ((uint32_t)s.y << 16);
+    p.plane_dir[a] = s.dir;
+    p.plane_hp[a] = (int8_t)s.hp;
+#pragma unroll
+    for (int q = 0; q < SLOTS - 1; ++q) {
+        p.bul_vel[q * EP + a] = s.bv[q + 1];
+        p.bul_pos[q * EP + a] = s.bp[q + 1];
+    }
+    // HBM slot 11 is never occupied between ticks (age 12 is removed); it stays zero from bs_create
+    if (g.k == 0) {  // first lane of each team owns its enemy's base record
+        p.base_hp[g.e * 2 + (1 - g.team)] = (int16_t)s.bhp_enemy;
+        if (base_pos_too) p.base_pos[g.e * 2 + (1 - g.team)] = (uint32_t)s.ebx | ((uint32_t)s.eby << 16);
+    }
+    if (g.i == 0) {
+        p.meta[g.e] = (uint32_t)s.tick | ((uint32_t)s.env_done << 16) | ((uint32_t)s.winner << 24);
+        p.episode[g.e] = s.episode;
+        p.ret[g.e * 2] = ret0; p.ret[g.e * 2 + 1] = ret1;
+    }
+}
+
+// Launch-level counter flush: warp-reduce the per-lane tallies, one atomic per warp per counter.
+__device__ __forceinline__ long long warp_sum(long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+
+template <int N>
+__device__ __forceinline__ void flush_tally(const Params &p, const Tally &tl) {
+    long long v[8] = {tl.wins_red, tl.wins_blue, tl.ties, tl.games, tl.ret_red, tl.ret_blue,
+                      tl.ticks, (long long)tl.ticks * (2 * N)};
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        long long t = warp_sum(v[c]);
+        if ((threadIdx.x & 31) == 0 && t != 0) atomicAdd(p.counters + c, (unsigned long long)t);
+    }
+}
+
+}  // namespace bs

@@ -1,0 +1,175 @@
+/*
+ * battlespace.h -- C ABI of libbattlespace.so, the B200 (sm_100a) batched implementation of the
+ * Deep-RL-Battlespace environment step + instinct policy.
+ *
+ * Each entry point replaces one piece of the reference's Python surface for this path (reference
+ * paths are relative to the reference root):
+ *
+ *   bs_create            parallel_env.__init__            envs/battle_env.py:73-184
+ *   bs_reset[_host]      parallel_env.reset               envs/battle_env.py:246-279
+ *                        (Base.reset / Plane.reset        envs/sprites.py:238-252, 74-91)
+ *   bs_step[_host]       parallel_env.step                envs/battle_env.py:281-381
+ *                        (process_action :383-424, Plane.forward/rotate sprites.py:93-141,
+ *                         Bullet.__init__/update sprites.py:293-351, observe :202-244,
+ *                         tie/win :469-496)
+ *   bs_instinct_actions  instinct Team.choose_actions     instinct/team.py:11-14, instinct/agent.py:10-62
+ *   bs_step_team         one game-loop iteration with the scripted team in-kernel
+ *                                                         main.py:179-181, evaluate.py:69-70
+ *   bs_rollout_fused     the whole inner game loop incl. ReplayBuffer.store_transition
+ *                                                         main.py:178-213, maddpg/buffer.py:25-47
+ *   bs_stats             env.team[c]['wins'], ties, total_games + report sums
+ *                                                         envs/battle_env.py:102-103,169-170; main.py:218-253
+ *   bs_get_state/bs_set_state   (no reference equivalent: checkpoint + parity injection)
+ *
+ * Conventions
+ *   - Plain C types only.  Unless a name ends in _host, every buffer is a CALLER-OWNED DEVICE
+ *     pointer on the handle's device and the call is asynchronous on `stream` (a cudaStream_t
+ *     passed as void*; NULL = the legacy default stream).  *_host entry points take host
+ *     pointers, do their own staged copies and return after the results are in host memory.
+ *   - Return value: 0 on success, negative BS_E_* otherwise; bs_last_error() gives the
+ *     message (thread local).  A handle is bound to one device and is not thread-safe.
+ *   - Agents: index i in [0,2N): red = [0,N), blue = [N,2N) (battle_env.py:106-108).
+ *     obs row length L = 3N+2 (battle_env.py:132).  A = 3 (continuous) or 4 (discrete).
+ *   - There is no CPU fallback: without a CUDA device every compute call fails with BS_E_CUDA.
+ *
+ * Random draws.  Either injected per call (`draws` arguments: the reference's own draws are
+ * replayed for parity) or Philox4x32-10 with
+ *     key     = (seed lo32, seed hi32)
+ *     counter = (g lo32, g hi32, episode, tick<<16 | agent<<8 | purpose),  g = env_offset + env
+ * so that env g sees the same stream however the envs are sharded over GPUs.
+ *   purpose 0 (agent tick): words w0..w3 ->
+ *       noise_u[k] = (w_k >> 8) / 2^24  (k=0..2)      instinct noise  instinct/agent.py:53
+ *       shoot_u    = ((w0&255)<<16 | (w1&255)<<8 | (w2&255)) / 2^24    instinct/agent.py:44
+ *       spread_u   = w3 / 2^32                        Bullet spread   envs/sprites.py:314
+ *       random policy: continuous a_k = 2*noise_u[k]-1, discrete a = w0 >> 30
+ *   purpose 1 (plane spawn, agent = plane): x, y, dir = lo + mulhi(w_k, hi-lo+1)
+ *   purpose 2 (base spawn): red x,y from w0,w1; blue x,y from w2,w3
+ *   `tick` is the env's step counter before the call, `episode` starts at 1.
+ * Injected unit draws are laid out [.., 5] doubles per agent: shoot_u, noise_u0..2, spread_u.
+ * Injected spawn draws are [E, 4+6N] int32 in the reference's call order (battle_env.py:257-268):
+ * red base x,y, blue base x,y, then x,y,dir for each red plane, then each blue plane.
+ */
+#ifndef BATTLESPACE_H
+#define BATTLESPACE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BS_VERSION 100
+#define BS_MAX_AGENTS 8     /* planes per team */
+#define BS_BULLET_SLOTS 12  /* per plane: a bullet is removed on its 12th update (sprites.py:334-337) */
+
+enum { BS_OK = 0, BS_E_INVALID = -1, BS_E_CUDA = -2, BS_E_UNSUPPORTED = -3 };
+enum { BS_ACT_I32 = 0, BS_ACT_F32 = 1, BS_ACT_F64 = 2, BS_ACT_NONE = 3 };
+enum { BS_POL_EXTERNAL = 0, BS_POL_RANDOM = 1, BS_POL_INSTINCT = 2, BS_POL_INSTINCT_FF = 3 };
+enum { BS_WINNER_NONE = 0, BS_WINNER_RED = 1, BS_WINNER_BLUE = 2, BS_WINNER_TIE = 3 };
+
+typedef struct bs_handle bs_handle;
+
+/* parallel_env(**kwargs) -- battle_env.py:73 (show / fps are host-side rendering options) */
+typedef struct bs_config {
+    int32_t n_agents;           /* planes per team, 1..BS_MAX_AGENTS */
+    int32_t continuous_actions; /* 0: Discrete(4), 1: Box(-1,1,(3,)) */
+    double hit_base_reward;
+    double hit_plane_reward;
+    double miss_punishment;
+    double die_punishment;
+    double lose_punishment;
+} bs_config;
+
+/* Replay ring in the row layout of maddpg/buffer.py:11-23 (float32; rows of the learner team). */
+typedef struct bs_replay {
+    float *state;       /* [capacity, N*L]   state_mem / actor_states[k] = columns k*L..(k+1)*L */
+    float *new_state;   /* [capacity, N*L] */
+    float *action;      /* [capacity, N, A]  action_mem[k] */
+    float *reward;      /* [capacity, N] */
+    uint8_t *done;      /* [capacity, N] */
+    int64_t capacity;   /* rows; 0 = write nothing */
+} bs_replay;
+
+/* Host-side view used by bs_get_state / bs_set_state (any pointer may be NULL = skip). */
+typedef struct bs_state_view {
+    int16_t *plane_x, *plane_y; /* [E,2N] rect centre */
+    double *plane_dir;          /* [E,2N] degrees */
+    int8_t *plane_hp;           /* [E,2N] */
+    int16_t *base_pos;          /* [E,2,2] (team, xy) */
+    int16_t *base_hp;           /* [E,2] may be negative */
+    int16_t *bullet_pos;        /* [E,2N,12,2] x,y ; -1,-1 = empty ; slot = age-1 */
+    int8_t *bullet_vel;         /* [E,2N,12,3] per-update integer step sx, sy and flags
+                                   (bit0 valid, bit1 sx exact, bit2 sy exact) */
+    int32_t *tick;              /* [E] */
+    uint8_t *env_done;          /* [E] */
+    int8_t *winner;             /* [E] BS_WINNER_* */
+    uint32_t *episode;          /* [E] */
+    double *team_return;        /* [E,2] running return of the current episode */
+} bs_state_view;
+
+int bs_version(void);
+const char *bs_last_error(void);
+
+int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int device, uint64_t seed,
+              bs_handle **out);
+int bs_destroy(bs_handle *h);
+
+/* Resets the envs with env_mask[e] != 0 (NULL = all).  draws: NULL (Philox) or [E,4+6N] int32.
+ * obs: NULL or [E,2N,L] float32, written for every env. */
+int bs_reset(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float *obs, void *stream);
+
+/* One tick for every env.  actions: BS_ACT_I32 [E,2N] | BS_ACT_F32 [E,2N,A] (continuous values,
+ * or discrete logits -> first argmax, battle_env.py:327-328) | BS_ACT_F64 [E,2N,3].
+ * BS_ACT_NONE (actions NULL) is the reference's "empty action dict": every running env ties
+ * (battle_env.py:309-313).
+ * draws: NULL or [E,2N,5].  Outputs (each may be NULL): obs [E,2N,L] f32, rew [E,2N] f32,
+ * done [E,2N] u8, env_done [E] u8, winner [E] i8.  Envs that are already done return their
+ * observation, zero rewards and their dones (battle_env.py:303-306); nothing auto-resets. */
+int bs_step(bs_handle *h, const void *actions, int action_dtype, const double *draws, float *obs,
+            float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner, void *stream);
+
+/* As bs_step, but the caller supplies only learner_team's actions ([E,N] / [E,N,A] / [E,N,3]);
+ * the other team is played in-kernel by other_policy (BS_POL_INSTINCT, _INSTINCT_FF or _RANDOM). */
+int bs_step_team(bs_handle *h, int learner_team, const void *team_actions, int action_dtype,
+                 int other_policy, const double *draws, float *obs, float *rew, uint8_t *done,
+                 uint8_t *env_done, int8_t *winner, void *stream);
+
+/* instinct Team.choose_actions for `team`: obs [E,2N,L] f32 in; actions_out [E,N,3] f64
+ * (continuous) or [E,N] i32 (discrete).  draws: NULL or [E,2N,5]. */
+int bs_instinct_actions(bs_handle *h, int team, const float *obs, const double *draws,
+                        void *actions_out, void *stream);
+
+/* T ticks in one launch: done envs reset themselves (Philox spawns), both teams act by policy
+ * (learner_team may be BS_POL_EXTERNAL with ext_actions [T,E,N,A] f32), and one replay row per
+ * env-tick is written at row (cursor + t*E + e) mod capacity.  replay may be NULL. */
+int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
+                     const float *ext_actions, const bs_replay *replay, int64_t cursor, void *stream);
+
+/* out[8] = {red wins, blue wins, ties, total_games, sum(red episode return)*2^20,
+ * sum(blue episode return)*2^20, env ticks, agent steps}; synchronises `stream`. */
+int bs_stats(bs_handle *h, int64_t out[8], void *stream);
+/* Device address of the same 8 int64 counters (for an NCCL all-reduce without a host hop). */
+int bs_stats_device(bs_handle *h, int64_t **dev_counters);
+
+int bs_get_state(bs_handle *h, const bs_state_view *host_view);
+int bs_set_state(bs_handle *h, const bs_state_view *host_view);
+
+/* ---- host-buffer entry points (same meaning; pinned staging + copies inside) ------------- */
+int bs_reset_host(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float *obs);
+int bs_step_host(bs_handle *h, const void *actions, int action_dtype, const double *draws,
+                 float *obs, float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner);
+int bs_step_team_host(bs_handle *h, int learner_team, const void *team_actions, int action_dtype,
+                      int other_policy, const double *draws, float *obs, float *rew, uint8_t *done,
+                      uint8_t *env_done, int8_t *winner);
+int bs_instinct_actions_host(bs_handle *h, int team, const float *obs, const double *draws,
+                             void *actions_out);
+/* ext_actions is a HOST buffer [T,E,N,A] (or NULL); replay rows stay on the device; the eight
+ * counters are copied back into stats_out (may be NULL). */
+int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
+                          const float *ext_actions, const bs_replay *replay, int64_t cursor,
+                          int64_t stats_out[8]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BATTLESPACE_H */

@@ -43,7 +43,7 @@
 #define BULLET_H 3
 
 enum { W_NONE = 0, W_RED = 1, W_BLUE = 2, W_TIE = 3 };
-enum { ACT_I32 = 0, ACT_F32 = 1, ACT_F64 = 2 };
+enum { ACT_I32 = 0, ACT_F32 = 1, ACT_F64 = 2, ACT_NONE = 3 };
 enum { POL_EXTERNAL = 0, POL_RANDOM = 1, POL_INSTINCT = 2, POL_INSTINCT_FF = 3 };
 enum { R_HIT_BASE = 0, R_HIT_PLANE = 1, R_MISS = 2, R_DIE = 3, R_LOSE = 4 };
 
@@ -331,14 +331,14 @@ typedef struct { int disc; double c[3]; } action_t;
  * agent's Bullet.__init__ would draw this tick (used only if it shoots).
  */
 static void env_step(oracle_t *o, int64_t e, const action_t *act, const double *spread_u,
-                     double *rew) {
+                     double *rew, int no_actions) {
     env_t *s = &o->env[e];
     const int N = o->N, P = o->P;
     for (int i = 0; i < P; ++i) rew[i] = 0;
     if (s->env_done) return;                                   /* :303-306 */
     int alive = 0;
     for (int i = 0; i < P; ++i) alive += s->in_agents[i];
-    if (alive == 0) { env_tie(o, s); return; }                  /* :309-313 */
+    if (no_actions || alive == 0) { env_tie(o, s); return; }    /* :309-313 */
     s->total_time += 0.1;                                      /* :316 */
     s->tick += 1;
     if (s->total_time >= o->max_time) { env_tie(o, s); return; } /* :319-323 */
@@ -470,6 +470,7 @@ static double clip1(double v) { return v < -1 ? -1 : (v > 1 ? 1 : v); } /* battl
 
 static void decode_action(const oracle_t *o, const void *actions, int dtype, int64_t idx, action_t *a) {
     a->disc = 0; a->c[0] = a->c[1] = a->c[2] = 0;
+    if (dtype == ACT_NONE) return;
     if (!o->cont) {
         if (dtype == ACT_I32) a->disc = ((const int32_t *)actions)[idx];
         else a->disc = argmax4((const float *)actions + idx * 4);
@@ -514,7 +515,7 @@ void bo_step(oracle_t *o, const void *actions, int dtype, const double *draws, f
             else { uint32_t w[4]; double u[5]; env_philox(o, e, s->episode, s->tick, i, PURPOSE_AGENT_TICK, w); agent_tick_units(w, u); su[i] = u[4]; }
         }
         int was_done = s->env_done;
-        env_step(o, e, act, su, r);
+        env_step(o, e, act, su, r, dtype == ACT_NONE);
         finish_tick(o, e, r, was_done);
         if (obs) observe_all(o, s, obs + (size_t)e * P * o->L);
         for (int i = 0; i < P; ++i) { if (rew) rew[e * P + i] = r[i]; if (done) done[e * P + i] = s->done[i]; }
@@ -591,7 +592,7 @@ void bo_rollout(oracle_t *o, int T, int learner, const int *pol, const float *ex
                         raw[i * 4 + k] = o->cont ? (float)act[i].c[k] : ext_actions[idx * A + k];
                 } else run_policy(o, pol[team], obs + (size_t)i * L, u, w[0], &act[i], raw + i * 4);
             }
-            env_step(o, e, act, su, r);
+            env_step(o, e, act, su, r, 0);
             finish_tick(o, e, r, 0);
             observe_all(o, s, obs2);
             if (capacity > 0) {

@@ -14,7 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
-ACT_I32, ACT_F32, ACT_F64 = 0, 1, 2
+ACT_I32, ACT_F32, ACT_F64, ACT_NONE = 0, 1, 2, 3
 POL_EXTERNAL, POL_RANDOM, POL_INSTINCT, POL_INSTINCT_FF = 0, 1, 2, 3
 SLOTS = 12
 
@@ -86,8 +86,10 @@ class OracleEnv:
         return obs
 
     def step(self, actions, draws=None):
-        a = np.ascontiguousarray(actions)
-        if a.dtype == np.int32:
+        a = None if actions is None else np.ascontiguousarray(actions)
+        if a is None:
+            dt = ACT_NONE
+        elif a.dtype == np.int32:
             dt = ACT_I32; assert a.size == self.E * self.P and not self.cont
         elif a.dtype == np.float32:
             dt = ACT_F32; assert a.size == self.E * self.P * self.A
