@@ -21,8 +21,6 @@ using namespace bs;
 // ------------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------------
-constexpr int BLOCK = 128;
-
 __device__ __forceinline__ long long global_warp() {
     return ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 }
@@ -40,26 +38,27 @@ __device__ __forceinline__ int argmax4(const float *v) {  // np.argmax: first ma
 template <int N>
 __global__ void __launch_bounds__(BLOCK) reset_kernel(Params p, const uint8_t *mask, const int32_t *draws, float *obs) {
     constexpr int P = 2 * N, L = 3 * N + 2;
+    __shared__ Ring rg;
     Geo<N> g(global_warp(), p.E);
     Lane<N> s;
     double ret0, ret1;
-    load_lane(p, g, s, ret0, ret1);
+    load_lane(p, g, s, rg, ret0, ret1);
     const bool need = g.valid && (mask == nullptr || mask[g.e] != 0);
     if (need) {
-        reset_lane(p, g, s, draws != nullptr, draws ? draws + g.e * (4 + 6 * N) : nullptr);
+        reset_lane(p, g, s, rg, draws != nullptr, draws ? draws + g.e * (4 + 6 * N) : nullptr);
         ret0 = ret1 = 0;
     }
     gather(g, s);
     if (obs != nullptr) {
         float o[L];
-        observe<N>(p, s, o);
+        observe<N>(s, o);
         if (g.valid) {
             float *dst = obs + (g.e * P + g.i) * L;
 #pragma unroll
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
     }
-    if (need) store_lane(p, g, s, ret0, ret1, true);
+    if (need) store_lane(p, g, s, rg, ret0, ret1, true);
 }
 
 struct StepArgs {
@@ -101,7 +100,7 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
             for (int c = 0; c < 4; ++c) raw[c] = c == adisc ? 1.0f : 0.0f;
         }
     } else if (pol == POL_INSTINCT || pol == POL_INSTINCT_FF) {
-        instinct<N, CONT>(p, o, u[0], u[1], u[2], u[3], adisc, a);
+        instinct<N, CONT>(o, u[0], u[1], u[2], u[3], adisc, a);
         if (CONT) {
             if (pol == POL_INSTINCT_FF) a[2] = 1.0;
 #pragma unroll
@@ -116,14 +115,15 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
 template <int N, bool CONT>
 __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
     constexpr int P = 2 * N, L = 3 * N + 2;
+    __shared__ Ring rg;
     Geo<N> g(global_warp(), p.E);
     Lane<N> s;
     double ret0, ret1;
-    load_lane(p, g, s, ret0, ret1);
+    load_lane(p, g, s, rg, ret0, ret1);
 
     float o[L];
     const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT;  // kernel-uniform
-    if (need_obs) { gather(g, s); observe<N>(p, s, o); }
+    if (need_obs) { gather(g, s); observe<N>(s, o); }
     else {
 #pragma unroll
         for (int c = 0; c < L; ++c) o[c] = -1.0f;
@@ -161,9 +161,9 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
 
     double rew;
     Tally tl;
-    tick<N, CONT>(p, g, s, adisc, a, spread_u, rew, ret0, ret1, tl, sa.dtype == ACT_NONE);
+    tick<N, CONT>(p, g, s, rg, adisc, a, spread_u, rew, ret0, ret1, tl, sa.dtype == ACT_NONE);
     if (sa.obs != nullptr) {
-        observe<N>(p, s, o);
+        observe<N>(s, o);
         if (g.valid) {
             float *dst = sa.obs + (g.e * P + g.i) * L;
 #pragma unroll
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
             if (sa.winner) sa.winner[g.e] = (int8_t)s.winner;
         }
     }
-    store_lane(p, g, s, ret0, ret1, false);
+    store_lane(p, g, s, rg, ret0, ret1, false);
     flush_tally<N>(p, tl);
 }
 
@@ -195,27 +195,29 @@ struct RolloutArgs {
 template <int N, bool CONT>
 __global__ void __launch_bounds__(BLOCK) rollout_kernel(Params p, RolloutArgs ra) {
     constexpr int L = 3 * N + 2, A = CONT ? 3 : 4;
+    __shared__ Ring rg;
     Geo<N> g(global_warp(), p.E);
     Lane<N> s;
     double ret0, ret1;
-    load_lane(p, g, s, ret0, ret1);
+    load_lane(p, g, s, rg, ret0, ret1);
     gather(g, s);
     float o[L];
-    observe<N>(p, s, o);
+    observe<N>(s, o);
     Tally tl;
     const int pol = ra.pol[g.team];
     const bool writer = g.valid && g.team == ra.learner && ra.rp.capacity > 0;
     long long row = 0;
     if (ra.rp.capacity > 0) row = (ra.cursor_mod + g.e % ra.rp.capacity) % ra.rp.capacity;
 
+#pragma unroll 1
     for (int t = 0; t < ra.T; ++t) {
         // auto-reset: the game loop's env.reset() -- main.py:148
         const bool need = g.valid && s.env_done;
         if (__any_sync(FULL, need)) {
-            if (need) { reset_lane(p, g, s, false, nullptr); ret0 = ret1 = 0; }
+            if (need) { reset_lane(p, g, s, rg, false, nullptr); ret0 = ret1 = 0; }
             gather(g, s);
             float o2[L];
-            observe<N>(p, s, o2);
+            observe<N>(s, o2);
             if (need) {
 #pragma unroll
                 for (int c = 0; c < L; ++c) o[c] = o2[c];
@@ -249,8 +251,8 @@ __global__ void __launch_bounds__(BLOCK) rollout_kernel(Params p, RolloutArgs ra
             }
         }
         double rew;
-        tick<N, CONT>(p, g, s, adisc, a, spread_u, rew, ret0, ret1, tl);
-        observe<N>(p, s, o);
+        tick<N, CONT>(p, g, s, rg, adisc, a, spread_u, rew, ret0, ret1, tl);
+        observe<N>(s, o);
         if (writer) {
             const long long ra_i = row * N + g.k;
             if (ra.rp.new_state) {
@@ -268,7 +270,7 @@ __global__ void __launch_bounds__(BLOCK) rollout_kernel(Params p, RolloutArgs ra
         row += ra.e_mod;
         if (row >= ra.rp.capacity) row -= ra.rp.capacity;
     }
-    store_lane(p, g, s, ret0, ret1, true);
+    store_lane(p, g, s, rg, ret0, ret1, true);
     flush_tally<N>(p, tl);
 }
 
@@ -291,11 +293,11 @@ __global__ void __launch_bounds__(BLOCK) instinct_kernel(Params p, int team, con
     } else {
         uint32_t w[4];
         const uint32_t m = p.meta[e];
-        env_philox(p, e, p.episode[e], (int)(m & 0xffff), i, PURPOSE_AGENT_TICK, w);
+        env_philox(p, e, p.episode[e], (int)(m & 0xfff), i, PURPOSE_AGENT_TICK, w);
         agent_tick_units(w, u);
     }
     int adisc; double a[3];
-    instinct<N, CONT>(p, o, u[0], u[1], u[2], u[3], adisc, a);
+    instinct<N, CONT>(o, u[0], u[1], u[2], u[3], adisc, a);
     if (CONT) {
         double *dst = (double *)out + t * 3;
         dst[0] = a[0]; dst[1] = a[1]; dst[2] = a[2];
@@ -411,11 +413,12 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     p.r_hit_base = cfg->hit_base_reward; p.r_hit_plane = cfg->hit_plane_reward;
     p.r_miss = cfg->miss_punishment; p.r_die = cfg->die_punishment; p.r_lose = cfg->lose_punishment;
     p.diag = std::sqrt(std::pow(1200.0, 2) + std::pow(800.0, 2));
+    if (p.diag != DIAG) { delete h; return fail(BS_E_INVALID, "host sqrt(1200^2+800^2) differs from the device constant"); }
     const size_t EP = (size_t)n_envs * h->P;
     int rc;
     if ((rc = dalloc(h, &p.plane_pos, EP)) || (rc = dalloc(h, &p.plane_dir, EP)) || (rc = dalloc(h, &p.plane_hp, EP)) ||
         (rc = dalloc(h, &p.base_pos, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.base_hp, (size_t)n_envs * 2)) ||
-        (rc = dalloc(h, &p.bul_pos, EP * SLOTS)) || (rc = dalloc(h, &p.bul_vel, EP * SLOTS)) ||
+        (rc = dalloc(h, &p.bul_pos, EP * SLOTS)) || (rc = dalloc(h, &p.bul_dlt, EP * SLOTS)) ||
         (rc = dalloc(h, &p.meta, (size_t)n_envs)) || (rc = dalloc(h, &p.episode, (size_t)n_envs)) ||
         (rc = dalloc(h, &p.ret, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.counters, 8))) {
         bs_destroy(h);
@@ -553,7 +556,8 @@ int bs_get_state(bs_handle *h, const bs_state_view *v) {
     DeviceGuard guard(h->device);
     CU(cudaDeviceSynchronize());
     const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
-    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), epi((size_t)E), bp(EP * SLOTS), bv(EP * SLOTS);
+    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), epi((size_t)E), bp(EP * SLOTS);
+    std::vector<int32_t> bd(EP * SLOTS);
     std::vector<double> dir(EP), ret((size_t)E * 2);
     std::vector<int8_t> hp(EP);
     std::vector<int16_t> bhp((size_t)E * 2);
@@ -564,26 +568,32 @@ int bs_get_state(bs_handle *h, const bs_state_view *v) {
     CU(cudaMemcpy(bpos.data(), p.base_pos, (size_t)E * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(bhp.data(), p.base_hp, (size_t)E * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(bp.data(), p.bul_pos, EP * SLOTS * 4, cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(bv.data(), p.bul_vel, EP * SLOTS * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(bd.data(), p.bul_dlt, EP * SLOTS * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(meta.data(), p.meta, (size_t)E * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(epi.data(), p.episode, (size_t)E * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(ret.data(), p.ret, (size_t)E * 16, cudaMemcpyDeviceToHost));
+    // ring slot -> age: the newest bullet (age 1) sits in slot head; exported index = age - 1
     for (size_t a = 0; a < EP; ++a) {
         if (v->plane_x) v->plane_x[a] = (int16_t)(pos[a] & 0xffff);
         if (v->plane_y) v->plane_y[a] = (int16_t)(pos[a] >> 16);
         if (v->plane_dir) v->plane_dir[a] = dir[a];
         if (v->plane_hp) v->plane_hp[a] = hp[a];
+        const int head = (int)((meta[a / P] >> 12) & 0xf);
         for (int q = 0; q < SLOTS; ++q) {
-            const uint32_t vel = bv[(size_t)q * EP + a], ps = bp[(size_t)q * EP + a];
-            const bool valid = (vel & BV_VALID) != 0;
+            const uint32_t ps = bp[(size_t)q * EP + a];
+            const int32_t dl = bd[(size_t)q * EP + a];
+            const bool valid = (ps & B_VALID) != 0;
+            const int o = (head - q + SLOTS) % SLOTS;
             if (v->bullet_pos) {
-                v->bullet_pos[(a * SLOTS + q) * 2] = valid ? (int16_t)(ps & 0xffff) : (int16_t)-1;
-                v->bullet_pos[(a * SLOTS + q) * 2 + 1] = valid ? (int16_t)(ps >> 16) : (int16_t)-1;
+                v->bullet_pos[(a * SLOTS + o) * 2] = valid ? (int16_t)((int)(ps & 0xffff) - 64) : (int16_t)-1;
+                v->bullet_pos[(a * SLOTS + o) * 2 + 1] = valid ? (int16_t)((int)((ps >> 16) & 0x1fff) - 64) : (int16_t)-1;
             }
             if (v->bullet_vel) {
-                v->bullet_vel[(a * SLOTS + q) * 3] = (int8_t)(vel & 0xff);
-                v->bullet_vel[(a * SLOTS + q) * 3 + 1] = (int8_t)((vel >> 8) & 0xff);
-                v->bullet_vel[(a * SLOTS + q) * 3 + 2] = (int8_t)((vel >> 16) & 0xff);
+                const int sx = (int16_t)(dl & 0xffff), sy = (dl - sx) >> 16;
+                v->bullet_vel[(a * SLOTS + o) * 3] = valid ? (int8_t)sx : (int8_t)0;
+                v->bullet_vel[(a * SLOTS + o) * 3 + 1] = valid ? (int8_t)sy : (int8_t)0;
+                v->bullet_vel[(a * SLOTS + o) * 3 + 2] =
+                    valid ? (int8_t)(1 | ((ps & B_XEXACT) ? 2 : 0) | ((ps & B_YEXACT) ? 4 : 0)) : (int8_t)0;
             }
         }
     }
@@ -593,7 +603,7 @@ int bs_get_state(bs_handle *h, const bs_state_view *v) {
             if (v->base_hp) v->base_hp[e * 2 + t] = bhp[e * 2 + t];
             if (v->team_return) v->team_return[e * 2 + t] = ret[e * 2 + t];
         }
-        if (v->tick) v->tick[e] = (int32_t)(meta[e] & 0xffff);
+        if (v->tick) v->tick[e] = (int32_t)(meta[e] & 0xfff);
         if (v->env_done) v->env_done[e] = (uint8_t)((meta[e] >> 16) & 0xff);
         if (v->winner) v->winner[e] = (int8_t)((meta[e] >> 24) & 0xff);
         if (v->episode) v->episode[e] = epi[e];
@@ -609,23 +619,29 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     DeviceGuard guard(h->device);
     CU(cudaDeviceSynchronize());
     const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
-    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), bp(EP * SLOTS), bv(EP * SLOTS);
+    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), bp(EP * SLOTS);
+    std::vector<int32_t> bd(EP * SLOTS);
     std::vector<int8_t> hp(EP);
+    // age -> ring slot with head = tick mod 12 (any head works as long as the slots agree with it)
     for (size_t a = 0; a < EP; ++a) {
         pos[a] = (uint32_t)(uint16_t)v->plane_x[a] | ((uint32_t)(uint16_t)v->plane_y[a] << 16);
-        for (int q = 0; q < SLOTS; ++q) {
-            const int8_t *vel = v->bullet_vel + (a * SLOTS + q) * 3;
-            const int16_t *ps = v->bullet_pos + (a * SLOTS + q) * 2;
-            const uint32_t w = (uint32_t)(uint8_t)vel[0] | ((uint32_t)(uint8_t)vel[1] << 8) | ((uint32_t)(uint8_t)vel[2] << 16);
-            const bool valid = (w & BV_VALID) != 0 && q < SLOTS - 1;
-            bv[(size_t)q * EP + a] = valid ? w : 0u;
-            bp[(size_t)q * EP + a] = valid ? ((uint32_t)(uint16_t)ps[0] | ((uint32_t)(uint16_t)ps[1] << 16)) : 0u;
+        const int head = (int)(v->tick[a / P] % SLOTS);
+        for (int o = 0; o < SLOTS; ++o) {
+            const int8_t *vel = v->bullet_vel + (a * SLOTS + o) * 3;
+            const int16_t *ps = v->bullet_pos + (a * SLOTS + o) * 2;
+            const bool valid = (vel[2] & 1) != 0 && o < SLOTS - 1;  // age 12 never survives a tick
+            const int q = (head - o + SLOTS) % SLOTS;
+            bp[(size_t)q * EP + a] = valid ? ((((uint32_t)(ps[0] + 64)) | ((uint32_t)(ps[1] + 64) << 16)) | B_VALID |
+                                              ((vel[2] & 2) ? B_XEXACT : 0u) | ((vel[2] & 4) ? B_YEXACT : 0u))
+                                           : 0u;
+            bd[(size_t)q * EP + a] = valid ? ((int32_t)vel[0] + (int32_t)vel[1] * 65536) : 0;
         }
     }
     for (int64_t e = 0; e < E; ++e) {
         for (int t = 0; t < 2; ++t)
             bpos[e * 2 + t] = (uint32_t)(uint16_t)v->base_pos[(e * 2 + t) * 2] | ((uint32_t)(uint16_t)v->base_pos[(e * 2 + t) * 2 + 1] << 16);
-        meta[e] = ((uint32_t)v->tick[e] & 0xffff) | ((uint32_t)(v->env_done[e] ? 1 : 0) << 16) | ((uint32_t)(uint8_t)v->winner[e] << 24);
+        meta[e] = ((uint32_t)v->tick[e] & 0xfff) | ((uint32_t)(v->tick[e] % SLOTS) << 12) |
+                  ((uint32_t)(v->env_done[e] ? 1 : 0) << 16) | ((uint32_t)(uint8_t)v->winner[e] << 24);
     }
     const Params &p = h->p;
     CU(cudaMemcpy(p.plane_pos, pos.data(), EP * 4, cudaMemcpyHostToDevice));
@@ -634,7 +650,7 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     CU(cudaMemcpy(p.base_pos, bpos.data(), (size_t)E * 8, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.base_hp, v->base_hp, (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.bul_pos, bp.data(), EP * SLOTS * 4, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(p.bul_vel, bv.data(), EP * SLOTS * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.bul_dlt, bd.data(), EP * SLOTS * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.meta, meta.data(), (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.episode, v->episode, (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.ret, v->team_return, (size_t)E * 16, cudaMemcpyHostToDevice));

@@ -1,10 +1,12 @@
 // tick.cuh -- device-side Battlespace tick for sm_100a.
 //
 // Mapping: one LANE per plane, one env per group of G = 2N consecutive lanes (red planes first),
-// K = 32 / G envs per warp.  Everything an env needs lives in the registers of its G lanes:
-// the lane's own plane, its own 12 bullet slots (an age-indexed shift register), and replicated
-// copies of the enemy planes / bases kept consistent with warp shuffles.  Control flow that
-// contains a shuffle is warp-uniform; per-env conditions are predicates.
+// K = 32 / G envs per warp.  A lane keeps its own plane in registers, a replicated view of the
+// enemy team (refreshed with warp shuffles) and its own 12 bullets in a shared-memory ring
+// (slot = spawn tick mod 12, one column per thread: bank-conflict free and dynamically indexable,
+// so the bullet loop stays ROLLED -- the first version of this file unrolled it over registers and
+// ran out of instruction cache: 132 KB of SASS per tick, stall_no_inst 55 %, profiles/r1_*).
+// Control flow that contains a shuffle is warp-uniform; per-env conditions are predicates.
 //
 // Arithmetic follows the reference operation by operation in IEEE double (compiled with
 // --fmad=false so that no multiply-add is contracted), see the citations on each function.
@@ -15,14 +17,18 @@
 namespace bs {
 
 constexpr int SLOTS = 12;
+constexpr int BLOCK = 128;
 constexpr unsigned FULL = 0xffffffffu;
 constexpr double PI = 3.14159265358979323846;
 constexpr double DEG2RAD = PI / 180.0;  // math.radians
 constexpr double RAD2DEG = 180.0 / PI;  // math.degrees
 constexpr double TWO_PI = 2 * PI;
+constexpr double DIAG = 1442.2205101855957;  // math.sqrt(1200**2 + 800**2), battle_env.py:230 (host asserts it)
 
-// bullet velocity word: sx (int8) | sy (int8) << 8 | flags << 16
-constexpr uint32_t BV_VALID = 1u << 16, BV_XEXACT = 1u << 17, BV_YEXACT = 1u << 18;
+// Bullet words.  pos: (x+64) | (y+64) << 16 | flags; the bias keeps both fields positive while a
+// bullet is one update past the field edge, so pos + dlt is ONE integer add (dlt = sx + sy*65536).
+constexpr uint32_t B_VALID = 1u << 31, B_XEXACT = 1u << 30, B_YEXACT = 1u << 29, B_POS = 0x1fffffffu;
+constexpr uint32_t B_BIAS = 64u | (64u << 16);
 
 enum { W_NONE = 0, W_RED = 1, W_BLUE = 2, W_TIE = 3 };
 enum { POL_EXTERNAL = 0, POL_RANDOM = 1, POL_INSTINCT = 2, POL_INSTINCT_FF = 3 };
@@ -36,26 +42,32 @@ struct Params {
     uint32_t seed_lo, seed_hi;
     int tie_tick;         // first step call whose accumulated 0.1s reach 10+2N (battle_env.py:316-319)
     double r_hit_base, r_hit_plane, r_miss, r_die, r_lose;
-    double diag;          // sqrt(1200^2 + 800^2), battle_env.py:230
+    double diag;          // == DIAG
     // SoA state (see DESIGN.md "Data layout in HBM")
     uint32_t *plane_pos;  // [E*2N]      x | y<<16
     double *plane_dir;    // [E*2N]
     int8_t *plane_hp;     // [E*2N]
     uint32_t *base_pos;   // [E*2]       x | y<<16
     int16_t *base_hp;     // [E*2]
-    uint32_t *bul_pos;    // [12][E*2N]  x | y<<16 (slot-major: coalesced per slot)
-    uint32_t *bul_vel;    // [12][E*2N]
-    uint32_t *meta;       // [E]         tick | env_done<<16 | winner<<24
+    uint32_t *bul_pos;    // [12][E*2N]  ring slot-major (coalesced per slot); word layout above
+    int32_t *bul_dlt;     // [12][E*2N]
+    uint32_t *meta;       // [E]         tick | head<<12 | env_done<<16 | winner<<24
     uint32_t *episode;    // [E]
     double *ret;          // [E*2]
     unsigned long long *counters;  // [8]
 };
 
+// The block's bullet ring in shared memory: [slot][thread].
+struct Ring {
+    uint32_t pos[SLOTS][BLOCK];
+    int32_t dlt[SLOTS][BLOCK];
+};
+
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al. 2011); counter layout in include/battlespace.h
-__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                              uint32_t k0, uint32_t k1, uint32_t (&w)[4]) {
-#pragma unroll
+__device__ __noinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                            uint32_t k0, uint32_t k1) {
+#pragma unroll 1
     for (int r = 0; r < 10; ++r) {
         uint32_t h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
         uint32_t h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
@@ -63,15 +75,16 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
         c0 = n0; c1 = l1; c2 = n2; c3 = l0;
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
-    w[0] = c0; w[1] = c1; w[2] = c2; w[3] = c3;
+    return make_uint4(c0, c1, c2, c3);
 }
 
 __device__ __forceinline__ void env_philox(const Params &p, long long e, uint32_t episode, int tick,
                                            int agent, int purpose, uint32_t (&w)[4]) {
     unsigned long long g = (unsigned long long)(p.env_offset + e);
-    philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), episode,
-                  ((uint32_t)tick << 16) | ((uint32_t)agent << 8) | (uint32_t)purpose, p.seed_lo,
-                  p.seed_hi, w);
+    uint4 r = philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), episode,
+                            ((uint32_t)tick << 16) | ((uint32_t)agent << 8) | (uint32_t)purpose,
+                            p.seed_lo, p.seed_hi);
+    w[0] = r.x; w[1] = r.y; w[2] = r.z; w[3] = r.w;
 }
 
 __device__ __forceinline__ int randint_from(uint32_t w, int lo, int hi) {
@@ -96,7 +109,6 @@ struct Geo {
     static constexpr int L = 3 * N + 2;   // observation length, battle_env.py:132
     int lane, i, team, k;                 // lane in warp; agent index; team; index in team
     int gb, tb, eb;                       // first lane of: my env, my team, the enemy team
-    unsigned gmask;                       // lanes of my env
     bool valid;                           // lane maps to an env < E
     long long e;                          // env index within the handle
 
@@ -112,8 +124,8 @@ struct Geo {
         gb = sub * G;
         tb = gb + team * N;
         eb = gb + (1 - team) * N;
-        gmask = (G == 32 ? FULL : ((1u << G) - 1u)) << gb;
     }
+    __device__ __forceinline__ unsigned gmask() const { return (G == 32 ? FULL : ((1u << G) - 1u)) << gb; }
 };
 
 // Registers of one lane.
@@ -121,14 +133,14 @@ template <int N>
 struct Lane {
     int x, y, hp;           // own plane: rect centre (sprites.py:84,131) and hit points
     double dir;             // own direction in degrees (sprites.py:67,99)
-    uint32_t bp[SLOTS];     // own bullets, index = age before this tick's update
-    uint32_t bv[SLOTS];
     int ebx, eby;           // enemy base centre
     int bhp_own, bhp_enemy; // base hit points (replicated over the group)
     int tick, env_done, winner;
+    int head;               // ring slot of the newest bullet (advances on every tick that moves bullets)
     uint32_t episode;
     // replicated view of the enemy team, refreshed by gather()
-    int ex[N], ey[N], ehp[N];
+    uint32_t exy[N];        // x | y << 16
+    uint32_t ehp4;          // 4 bits of hp per enemy
     unsigned am;            // bit j: enemy j is in self.agents (hp > 0)
 };
 
@@ -136,42 +148,44 @@ template <int N>
 __device__ __forceinline__ void gather(const Geo<N> &g, Lane<N> &s) {
     // x 11 bits | y 10 bits | hp 3 bits
     uint32_t mine = (uint32_t)s.x | ((uint32_t)s.y << 11) | ((uint32_t)(s.hp > 0 ? s.hp : 0) << 21);
-    s.am = 0;
+    s.am = 0; s.ehp4 = 0;
 #pragma unroll
     for (int j = 0; j < N; ++j) {
         uint32_t v = __shfl_sync(FULL, mine, g.eb + j);
-        s.ex[j] = v & 0x7ff; s.ey[j] = (v >> 11) & 0x3ff; s.ehp[j] = (v >> 21) & 7;
-        s.am |= (s.ehp[j] > 0 ? 1u : 0u) << j;
+        s.exy[j] = (v & 0x7ffu) | (((v >> 11) & 0x3ffu) << 16);
+        uint32_t hp = (v >> 21) & 7u;
+        s.ehp4 |= hp << (4 * j);
+        s.am |= (hp ? 1u : 0u) << j;
     }
 }
 
-// rel_angle / 360 -- battle_env.py:38-52,231 ; dist / diag * 2 - 1 -- battle_env.py:54-58,230
-__device__ __forceinline__ void pair_obs(const Params &p, int x0, int y0, double a0, int x1, int y1,
-                                         float &od, float &oa) {
-    int dx = x0 - x1, dy = y0 - y1;
+// rel_angle / 360 -- battle_env.py:38-52,231 ; dist / diag * 2 - 1 -- battle_env.py:54-58,230.
+// One out-of-line copy per kernel (instruction-cache footprint); returns (od, oa).
+__device__ __noinline__ float2 pair_obs(int dx, int dy, double a0) {
     double d = sqrt((double)(dx * dx + dy * dy));
-    od = (float)(d / p.diag * 2 - 1);
+    float od = (float)(d / DIAG * 2 - 1);
     double r = atan2((double)dy, (double)dx);
     if (r < 0) r += TWO_PI;                    // Python float %: fmod plus sign fix-up
     double degs = r * RAD2DEG;
     double rel = 180 + a0 - (360 - degs);
     if (rel < -180) rel += 360;
     if (rel > 180) rel -= 360;
-    oa = (float)(rel / 360);
+    return make_float2(od, (float)(rel / 360));
 }
 
 // observe -- battle_env.py:202-244, for the lane's own plane; needs a fresh gather().
 template <int N>
-__device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float (&o)[3 * N + 2]) {
+__device__ __forceinline__ void observe(const Lane<N> &s, float (&o)[3 * N + 2]) {
 #pragma unroll
     for (int c = 0; c < 3 * N + 2; ++c) o[c] = -1.0f;
     if (s.hp > 0) {
-        pair_obs(p, s.x, s.y, s.dir, s.ebx, s.eby, o[0], o[1]);
+        float2 r = pair_obs(s.x - s.ebx, s.y - s.eby, s.dir);
+        o[0] = r.x; o[1] = r.y;
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-            if (s.ehp[j] > 0) {
-                o[2 + 3 * j] = 1.0f;
-                pair_obs(p, s.x, s.y, s.dir, s.ex[j], s.ey[j], o[3 + 3 * j], o[4 + 3 * j]);
+            if ((s.am >> j) & 1u) {
+                r = pair_obs(s.x - (int)(s.exy[j] & 0xffffu), s.y - (int)(s.exy[j] >> 16), s.dir);
+                o[2 + 3 * j] = 1.0f; o[3 + 3 * j] = r.x; o[4 + 3 * j] = r.y;
             }
         }
     }
@@ -180,14 +194,14 @@ __device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float
 // InstinctAgent.choose_action -- instinct/agent.py:10-62 (float32 obs decoded in double:
 // numpy 1.23.1 promotion).  Continuous: a[0..2]; discrete: adisc.
 template <int N, bool CONT>
-__device__ __forceinline__ void instinct(const Params &p, const float (&o)[3 * N + 2], double shoot_u,
+__device__ __forceinline__ void instinct(const float (&o)[3 * N + 2], double shoot_u,
                                          double n0, double n1, double n2, int &adisc, double (&a)[3]) {
-    double td = ((double)o[0] + 1) / 2 * p.diag;
+    double td = ((double)o[0] + 1) / 2 * DIAG;
     double ta = (double)o[1] * 360;
     double best = td * fabs(ta);  // base wins ties: replaced only by a strictly smaller score
 #pragma unroll
     for (int j = 0; j < N; ++j) {
-        double dj = ((double)o[3 + 3 * j] + 1) / 2 * p.diag;
+        double dj = ((double)o[3 + 3 * j] + 1) / 2 * DIAG;
         double aj = (double)o[4 + 3 * j] * 360;
         double sc = (o[2 + 3 * j] == 1.0f) ? dj * fabs(aj) : 1000000.0;
         if (sc < best) { best = sc; td = dj; ta = aj; }
@@ -195,7 +209,7 @@ __device__ __forceinline__ void instinct(const Params &p, const float (&o)[3 * N
     if (CONT) {
         double a2 = 0;
         if (td < 500.0 / 3 * 2 && fabs(ta) < 20) a2 = shoot_u < 0.6 ? 1.0 : -1.0;
-        double a0 = td / p.diag * 2 - 1;
+        double a0 = td / DIAG * 2 - 1;
         double v = -ta / 35, a1;
         if (ta > 0) a1 = v > -1 ? v : -1; else a1 = v < 1 ? v : 1;
         double t0 = a0 + (-0.15 + (0.15 - -0.15) * n0);
@@ -211,15 +225,21 @@ __device__ __forceinline__ void instinct(const Params &p, const float (&o)[3 * N
     }
 }
 
-// Plane.forward + clamp -- sprites.py:35-42,123-141 (rect.center = floats: C cast, then the
-// screen clamp; centre x in [25,1175], y in [24,776] for the 50x48 sprite)
-__device__ __forceinline__ void plane_forward(int &x, int &y, double dir, double speed) {
+// (cos, sin)(-radians(dir)) -- calc_new_xy, sprites.py:35-42.  Out of line: two call sites per tick.
+__device__ __noinline__ double2 cos_sin_dir(double dir) {
     double rad = -(dir * DEG2RAD);
     double sn, cs;
     sincos(rad, &sn, &cs);
+    return make_double2(cs, sn);
+}
+
+// Plane.forward + clamp -- sprites.py:123-141 (rect.center = floats: C cast, then the
+// screen clamp; centre x in [25,1175], y in [24,776] for the 50x48 sprite)
+__device__ __forceinline__ void plane_forward(int &x, int &y, double dir, double speed) {
+    double2 cssn = cos_sin_dir(dir);
     double st = speed * 0.1;
-    int nx = (int)((double)x + st * cs);
-    int ny = (int)((double)y + st * sn);
+    int nx = (int)((double)x + st * cssn.x);
+    int ny = (int)((double)y + st * cssn.y);
     x = min(max(nx, 25), 1175);
     y = min(max(ny, 24), 776);
 }
@@ -238,112 +258,161 @@ struct Tally {
     long long ret_red = 0, ret_blue = 0;
 };
 
+// Packed rect test.  D = (bullet fields) - (target fields): both 16-bit fields must land in
+// [0, rx) x [0, ry).  A negative low field borrows from the high one, but then the low test has
+// already failed; a negative high field makes D huge as unsigned.  (colliderect closed forms,
+// plane -28<dx<28, -26<dy<25; base -34<dx<34, -33<dy<32.)
+__device__ __forceinline__ bool rect_hit(uint32_t D, uint32_t rx, uint32_t ry) {
+    return (D & 0xffffu) < rx && D < (ry << 16);
+}
+constexpr uint32_t PLANE_OFF = B_BIAS - (27u | (25u << 16));  // pos - PLANE_OFF: fields x+27, y+25
+
+template <int N>
+__device__ __forceinline__ unsigned plane_overlaps(const Lane<N> &s, uint32_t pos) {
+    const uint32_t Pp = (pos & B_POS) - PLANE_OFF;
+    unsigned cm = 0;
+#pragma unroll
+    for (int j = 0; j < N; ++j) cm |= (rect_hit(Pp - s.exy[j], 55u, 50u) ? 1u : 0u) << j;
+    return cm;
+}
+
 // One env tick -- parallel_env.step, battle_env.py:281-381.
 //   adisc / a[3] : this lane's decoded action (clipped / argmax-ed);  spread_u : its Bullet draw.
 //   rew          : this lane's reward for the tick (double, reference accumulation order).
 // On return s holds the new state and gather() data is current (positions after the move,
 // enemy hp after the bullet loop), so observe() can be called directly.
 template <int N, bool CONT>
-__device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &s, int adisc,
+__device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &s, Ring &rg, int adisc,
                                      const double (&a)[3], double spread_u, double &rew,
                                      double &ret0, double &ret1, Tally &tl, bool no_actions = false) {
+    const int tid = threadIdx.x;
     rew = 0.0;
     const bool active = g.valid && !s.env_done;                        // :303-306
     const unsigned alive_b = __ballot_sync(FULL, active && s.hp > 0);
-    const bool any_alive = !no_actions && (alive_b & g.gmask) != 0;    // len(actions) == 0 also ties
+    const bool any_alive = !no_actions && (alive_b & g.gmask()) != 0;  // len(actions) == 0 also ties
     const bool tie_now = active && !any_alive;                         // :309-313
     const bool adv = active && any_alive;
     s.tick += adv ? 1 : 0;                                             // :316
     const bool time_tie = adv && s.tick >= p.tie_tick;                 // :319-323
     const bool run = adv && !time_tie;
+    if (run) s.head = s.head == SLOTS - 1 ? 0 : s.head + 1;
+    const int h = s.head;
 
     // ---- actions of the planes that are alive, :325-329 + process_action :383-424 -----------
     const int x0 = s.x, y0 = s.y;
     const double d0 = s.dir;
     bool shoot = false;
     if (run && s.hp > 0) {
+        double mdir = s.dir, speed = 215;
+        bool move = true;
         if (CONT) {
-            double speed = ((a[0] + 1) / 2) * (275 - 200) + 200;
-            plane_forward(s.x, s.y, s.dir, speed);
-            s.dir = plane_rotate(s.dir, a[1] * 35);
-            shoot = a[2] > 0;
-        } else if (adisc >= 0 && adisc <= 3) {
+            speed = ((a[0] + 1) / 2) * (275 - 200) + 200;
+        } else {
+            move = adisc >= 0 && adisc <= 3;
             shoot = adisc == 1;
-            if (adisc == 2) s.dir = plane_rotate(s.dir, 15);
-            if (adisc == 3) s.dir = plane_rotate(s.dir, -15);
-            plane_forward(s.x, s.y, s.dir, 215);
+            if (adisc == 2) mdir = plane_rotate(s.dir, 15);
+            if (adisc == 3) mdir = plane_rotate(s.dir, -15);
         }
+        if (move) plane_forward(s.x, s.y, mdir, speed);
+        if (CONT) { s.dir = plane_rotate(s.dir, a[1] * 35); shoot = a[2] > 0; }
+        else s.dir = mdir;
     }
     // Bullet.__init__ -- sprites.py:293-318.  From here on the bullet is integer: its per-update
     // displacement d = 45*cos/sin is constant, and trunc(int + d) == int + floor(d) except that
     // a result in (-1,0) truncates to 0 (flagged "exact" when d itself is an integer).
-    s.bv[0] = 0;
-    if (shoot) {
-        double bd = d0 + (spread_u * 8 - 4);
-        double rad = -(bd * DEG2RAD);
-        double sn, cs;
-        sincos(rad, &sn, &cs);
-        double ddx = (450 * 0.1) * cs, ddy = (450 * 0.1) * sn;
-        double fx = floor(ddx), fy = floor(ddy);
-        s.bp[0] = (uint32_t)x0 | ((uint32_t)y0 << 16);
-        s.bv[0] = ((uint32_t)(int)fx & 0xffu) | (((uint32_t)(int)fy & 0xffu) << 8) | BV_VALID |
-                  (fx == ddx ? BV_XEXACT : 0u) | (fy == ddy ? BV_YEXACT : 0u);
+    if (run) {
+        uint32_t P = 0;
+        int32_t D = 0;
+        if (shoot) {
+            double2 cssn = cos_sin_dir(d0 + (spread_u * 8 - 4));
+            double ddx = (450 * 0.1) * cssn.x, ddy = (450 * 0.1) * cssn.y;
+            double fx = floor(ddx), fy = floor(ddy);
+            P = (((uint32_t)x0 | ((uint32_t)y0 << 16)) + B_BIAS) | B_VALID | (fx == ddx ? B_XEXACT : 0u) |
+                (fy == ddy ? B_YEXACT : 0u);
+            D = (int)fx + (int)fy * 65536;
+        }
+        rg.pos[h][tid] = P;
+        rg.dlt[h][tid] = D;
     }
 
     gather(g, s);  // enemy positions after the move, hp before the bullet loop
 
     // ---- bullets, oldest first; same age: agent order -- :332-360, sprites.py:321-351 --------
+    // Phase 1 (no ordering needed): move every bullet, settle misses and base hits, and flag the
+    // bullets that overlap an enemy plane alive at the start of the loop.  ev: 2 bits per age
+    // index a (0 = oldest): 1 miss, 2 base hit, 3 plane hit.
+    unsigned ev = 0, cand = 0;
     int base_hits = 0;
-#pragma unroll
-    for (int q = SLOTS - 1; q >= 0; --q) {
-        const uint32_t v = s.bv[q];
-        const bool bvalid = run && (v & BV_VALID);
-        int bx = (int)(s.bp[q] & 0xffffu) + (int)(int8_t)(v & 0xffu);
-        int by = (int)(s.bp[q] >> 16) + (int)(int8_t)((v >> 8) & 0xffu);
-        if (bx == -1 && !(v & BV_XEXACT)) bx = 0;
-        if (by == -1 && !(v & BV_YEXACT)) by = 0;
-        const bool miss = (q == SLOTS - 1) || (unsigned)bx > 1200u || (unsigned)by > 800u;
-        // colliderect closed forms: base -34<dx<34, -33<dy<32; plane -28<dx<28, -26<dy<25
-        const bool bhit = !miss && (unsigned)(bx - s.ebx + 33) < 67u && (unsigned)(by - s.eby + 32) < 64u;
+    const uint32_t baseT = (((uint32_t)(s.ebx - 33)) | ((uint32_t)(s.eby - 32) << 16)) + B_BIAS;
+    int slot = h + 1 == SLOTS ? 0 : h + 1;
+    if (run && (rg.pos[slot][tid] & B_VALID)) {  // 12th update: dist_travelled >= 500, sprites.py:334-337
+        ev = 1u;
+        rg.pos[slot][tid] = 0;
+    }
+#pragma unroll 1
+    for (int ai = 1; ai < SLOTS; ++ai) {
+        slot = slot + 1 == SLOTS ? 0 : slot + 1;
+        uint32_t P = rg.pos[slot][tid];
+        if (run && (P & B_VALID)) {
+            P += (uint32_t)rg.dlt[slot][tid];
+            uint32_t Q = (P & B_POS) - B_BIAS;  // fields x, y
+            bool miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
+            if (miss) {  // corner: a coordinate of -1 that came from a sum in (-1,0) is 0 (C cast)
+                if ((Q & 0xffffu) == 0xffffu && !(P & B_XEXACT)) { P += 1u; Q += 1u; }
+                if ((Q >> 16) == 0xffffu && !(P & B_YEXACT)) { P += 0x10000u; Q += 0x10000u; }
+                miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
+            }
+            if (miss) { ev |= 1u << (2 * ai); P = 0; }
+            else if (rect_hit((P & B_POS) - baseT, 67u, 64u)) { ev |= 2u << (2 * ai); base_hits += 1; P = 0; }
+            else if (plane_overlaps<N>(s, P) & s.am) cand |= 1u << ai;
+            rg.pos[slot][tid] = P;
+        }
+    }
+    // Phase 2 (ordered, only for ages where some lane of the warp has a candidate): resolve the N
+    // same-age bullets of each team in agent order; a plane that dies is invisible to later ones.
+    int died_ai = -1;
+    unsigned allc = __reduce_or_sync(FULL, cand);
+    while (allc) {
+        const int ai = __ffs(allc) - 1;
+        allc &= allc - 1;
+        int sl = h + 1 + ai;
+        if (sl >= SLOTS) sl -= SLOTS;
         unsigned cm = 0;
-#pragma unroll
-        for (int j = 0; j < N; ++j)
-            cm |= (((unsigned)(bx - s.ex[j] + 27) < 55u && (unsigned)(by - s.ey[j] + 25) < 50u) ? 1u : 0u) << j;
-        if (!(bvalid && !miss && !bhit)) cm = 0;
-        int cand = -1;
-        bool died_now = false;
-        if (__any_sync(FULL, (cm & s.am) != 0)) {
-            // Somebody in the warp hits a plane at this age.  Resolve the N same-age bullets of
-            // each team in agent order; a plane that dies is invisible to the later ones.
-#pragma unroll
-            for (int kk = 0; kk < N; ++kk) {
-                unsigned m = cm & s.am;
-                int c_me = m ? (__ffs(m) - 1) : -1;
-                int c_team = __shfl_sync(FULL, c_me, g.tb + kk);   // teammate kk's victim
-                int c_foe = __shfl_sync(FULL, c_me, g.eb + kk);    // enemy kk's victim
-                if (kk == g.k) cand = c_me;
-#pragma unroll
-                for (int j = 0; j < N; ++j)
-                    if (c_team == j) { s.ehp[j] -= 1; if (s.ehp[j] <= 0) s.am &= ~(1u << j); }
-                if (g.valid && c_foe == g.k && s.hp > 0) { s.hp -= 1; died_now = died_now || s.hp <= 0; }
+        if ((cand >> ai) & 1u) cm = plane_overlaps<N>(s, rg.pos[sl][tid]);
+        int victim = -1;
+#pragma unroll 1
+        for (int kk = 0; kk < N; ++kk) {
+            const unsigned m = cm & s.am;
+            const int c_me = m ? (__ffs(m) - 1) : -1;
+            const int c_team = __shfl_sync(FULL, c_me, g.tb + kk);   // teammate kk's victim
+            const int c_foe = __shfl_sync(FULL, c_me, g.eb + kk);    // enemy kk's victim
+            if (kk == g.k) victim = c_me;
+            if (c_team >= 0) {
+                s.ehp4 -= 1u << (4 * c_team);
+                if (((s.ehp4 >> (4 * c_team)) & 0xfu) == 0) s.am &= ~(1u << c_team);
+            }
+            if (g.valid && c_foe == g.k && s.hp > 0) {
+                s.hp -= 1;
+                if (s.hp <= 0 && died_ai < 0) died_ai = ai;
             }
         }
-        const bool removed = bvalid && (miss || bhit || cand >= 0);
-        const double own = miss ? p.r_miss : (bhit ? p.r_hit_base : p.r_hit_plane);
-        base_hits += (bvalid && bhit) ? 1 : 0;
-        // reference order inside one age: red bullets first, so a blue victim's die_punishment
-        // precedes its own bullet's outcome and a red victim's follows it
-        if (died_now && g.team == 1) rew += p.r_die;
-        if (removed) rew += own;
-        if (died_now && g.team == 0) rew += p.r_die;
-        if (removed) s.bv[q] = 0;
-        else if (bvalid) s.bp[q] = (uint32_t)bx | ((uint32_t)by << 16);
+        if (victim >= 0) { ev |= 3u << (2 * ai); rg.pos[sl][tid] = 0; }
     }
-    // age the shift register
-    if (run) {
-#pragma unroll
-        for (int q = SLOTS - 1; q > 0; --q) { s.bp[q] = s.bp[q - 1]; s.bv[q] = s.bv[q - 1]; }
-        s.bv[0] = 0;
+    // Rewards in the reference's accumulation order (:337-360): per age, own bullet outcome; a
+    // victim's die_punishment precedes its own same-age outcome for blue (red bullets come first
+    // in the list) and follows it for red.
+    {
+        unsigned e2 = ev;
+        int da = died_ai;
+        while (e2 != 0 || da >= 0) {
+            const int ae = e2 ? ((__ffs(e2) - 1) >> 1) : 64;
+            if (da >= 0 && (da < ae || (da == ae && g.team == 1))) { rew += p.r_die; da = -1; }
+            else {
+                const unsigned code = (e2 >> (2 * ae)) & 3u;
+                rew += code == 1u ? p.r_miss : (code == 2u ? p.r_hit_base : p.r_hit_plane);
+                e2 &= ~(3u << (2 * ae));
+            }
+        }
     }
     // base damage: no alive check, hp may go negative
     int mine_total = 0, foe_total = 0;
@@ -388,7 +457,7 @@ __device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &
 // parallel_env.reset for one lane -- battle_env.py:246-279, sprites.py:74-91,238-252.
 // d_* are this lane's spawn values when injected (inj=true), else Philox.
 template <int N>
-__device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lane<N> &s, bool inj,
+__device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lane<N> &s, Ring &rg, bool inj,
                                            const int32_t *draws /* this env's [4+6N] or null */) {
     s.episode += 1;
     int rbx, rby, bbx, bby, px, py, pd;
@@ -410,21 +479,25 @@ __device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lan
     s.ebx = g.team == 0 ? bbx : rbx; s.eby = g.team == 0 ? bby : rby;
     s.bhp_own = s.bhp_enemy = 5 * N;                                                // battle_env.py:91
 #pragma unroll
-    for (int q = 0; q < SLOTS; ++q) { s.bp[q] = 0; s.bv[q] = 0; }
-    s.tick = 0; s.env_done = 0; s.winner = W_NONE;
+    for (int q = 0; q < SLOTS; ++q) rg.pos[q][threadIdx.x] = 0;
+    s.tick = 0; s.head = 0; s.env_done = 0; s.winner = W_NONE;
 }
 
-// ---- state <-> registers ------------------------------------------------------------------------
+// ---- state <-> registers / shared ring --------------------------------------------------------
 template <int N>
-__device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane<N> &s, double &ret0,
+__device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane<N> &s, Ring &rg, double &ret0,
                                           double &ret1) {
     constexpr int P = 2 * N;
-    s.x = s.y = 0; s.hp = 0; s.dir = 0; s.ebx = s.eby = 0; s.bhp_own = s.bhp_enemy = 0;
-    s.tick = 0; s.env_done = 1; s.winner = 0; s.episode = 0; ret0 = ret1 = 0;
-#pragma unroll
-    for (int q = 0; q < SLOTS; ++q) { s.bp[q] = 0; s.bv[q] = 0; }
+    const int tid = threadIdx.x;
+    s.x = s.y = 0; s.hp = 0; s.dir = 0; s.ebx = s.eby = 64; s.bhp_own = s.bhp_enemy = 0;
+    s.tick = 0; s.head = 0; s.env_done = 1; s.winner = 0; s.episode = 0; ret0 = ret1 = 0;
     if (g.valid) {
         const long long a = g.e * P + g.i, EP = p.E * P;
+#pragma unroll
+        for (int q = 0; q < SLOTS; ++q) {
+            rg.pos[q][tid] = p.bul_pos[q * EP + a];
+            rg.dlt[q][tid] = p.bul_dlt[q * EP + a];
+        }
         uint32_t pos = p.plane_pos[a];
         s.x = pos & 0xffff; s.y = pos >> 16;
         s.dir = p.plane_dir[a];
@@ -434,38 +507,36 @@ __device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane
         s.bhp_own = p.base_hp[g.e * 2 + g.team];
         s.bhp_enemy = p.base_hp[g.e * 2 + (1 - g.team)];
         uint32_t m = p.meta[g.e];
-        s.tick = m & 0xffff; s.env_done = (m >> 16) & 0xff; s.winner = (m >> 24) & 0xff;
+        s.tick = m & 0xfff; s.head = (m >> 12) & 0xf; s.env_done = (m >> 16) & 0xff; s.winner = (m >> 24) & 0xff;
         s.episode = p.episode[g.e];
-#pragma unroll
-        for (int q = 0; q < SLOTS - 1; ++q) {  // HBM slot q holds age q+1; ages 1..11 exist between ticks
-            s.bv[q + 1] = p.bul_vel[q * EP + a];
-            s.bp[q + 1] = p.bul_pos[q * EP + a];
-        }
         if (g.i == 0) { ret0 = p.ret[g.e * 2]; ret1 = p.ret[g.e * 2 + 1]; }
+    } else {
+#pragma unroll
+        for (int q = 0; q < SLOTS; ++q) { rg.pos[q][tid] = 0; rg.dlt[q][tid] = 0; }
     }
 }
 
 template <int N>
-__device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, const Lane<N> &s,
+__device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, const Lane<N> &s, const Ring &rg,
                                            double ret0, double ret1, bool base_pos_too) {
     constexpr int P = 2 * N;
     if (!g.valid) return;
+    const int tid = threadIdx.x;
     const long long a = g.e * P + g.i, EP = p.E * P;
     p.plane_pos[a] = (uint32_t)s.x | ((uint32_t)s.y << 16);
     p.plane_dir[a] = s.dir;
     p.plane_hp[a] = (int8_t)s.hp;
 #pragma unroll
-    for (int q = 0; q < SLOTS - 1; ++q) {
-        p.bul_vel[q * EP + a] = s.bv[q + 1];
-        p.bul_pos[q * EP + a] = s.bp[q + 1];
+    for (int q = 0; q < SLOTS; ++q) {
+        p.bul_pos[q * EP + a] = rg.pos[q][tid];
+        p.bul_dlt[q * EP + a] = rg.dlt[q][tid];
     }
-    // HBM slot 11 is never occupied between ticks (age 12 is removed); it stays zero from bs_create
     if (g.k == 0) {  // first lane of each team owns its enemy's base record
         p.base_hp[g.e * 2 + (1 - g.team)] = (int16_t)s.bhp_enemy;
         if (base_pos_too) p.base_pos[g.e * 2 + (1 - g.team)] = (uint32_t)s.ebx | ((uint32_t)s.eby << 16);
     }
     if (g.i == 0) {
-        p.meta[g.e] = (uint32_t)s.tick | ((uint32_t)s.env_done << 16) | ((uint32_t)s.winner << 24);
+        p.meta[g.e] = (uint32_t)s.tick | ((uint32_t)s.head << 12) | ((uint32_t)s.env_done << 16) | ((uint32_t)s.winner << 24);
         p.episode[g.e] = s.episode;
         p.ret[g.e * 2] = ret0; p.ret[g.e * 2 + 1] = ret1;
     }
