@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbattlespace.so")
+LIB_PATH = os.environ.get("BATTLESPACE_LIB") or os.path.join(_HERE, "libbattlespace.so")  # override: kernel A/B runs
 
 BS_OK, BS_E_INVALID, BS_E_CUDA, BS_E_UNSUPPORTED = 0, -1, -2, -3
 ACT_I32, ACT_F32, ACT_F64, ACT_NONE = 0, 1, 2, 3

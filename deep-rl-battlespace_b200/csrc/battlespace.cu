@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -51,7 +52,7 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(Params p, const uint8_t *m
     gather(g, s);
     if (obs != nullptr) {
         float o[L];
-        observe<N>(s, o);
+        observe<N>(p, s, o);
         if (g.valid) {
             float *dst = obs + (g.e * P + g.i) * L;
 #pragma unroll
@@ -123,7 +124,7 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
 
     float o[L];
     const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT;  // kernel-uniform
-    if (need_obs) { gather(g, s); observe<N>(s, o); }
+    if (need_obs) { gather(g, s); observe<N>(p, s, o); }
     else {
 #pragma unroll
         for (int c = 0; c < L; ++c) o[c] = -1.0f;
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
     Tally tl;
     tick<N, CONT>(p, g, s, rg, adisc, a, spread_u, rew, ret0, ret1, tl, sa.dtype == ACT_NONE);
     if (sa.obs != nullptr) {
-        observe<N>(s, o);
+        observe<N>(p, s, o);
         if (g.valid) {
             float *dst = sa.obs + (g.e * P + g.i) * L;
 #pragma unroll
@@ -192,8 +193,11 @@ struct RolloutArgs {
     long long e_mod;      // E % capacity
 };
 
+#ifndef ROLLOUT_MIN_BLOCKS
+#define ROLLOUT_MIN_BLOCKS 8
+#endif
 template <int N, bool CONT>
-__global__ void __launch_bounds__(BLOCK) rollout_kernel(Params p, RolloutArgs ra) {
+__global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Params p, RolloutArgs ra) {
     constexpr int L = 3 * N + 2, A = CONT ? 3 : 4;
     __shared__ Ring rg;
     Geo<N> g(global_warp(), p.E);
@@ -202,7 +206,7 @@ __global__ void __launch_bounds__(BLOCK) rollout_kernel(Params p, RolloutArgs ra
     load_lane(p, g, s, rg, ret0, ret1);
     gather(g, s);
     float o[L];
-    observe<N>(s, o);
+    observe<N>(p, s, o);
     Tally tl;
     const int pol = ra.pol[g.team];
     const bool writer = g.valid && g.team == ra.learner && ra.rp.capacity > 0;
@@ -217,7 +221,7 @@ __global__ void __launch_bounds__(BLOCK) rollout_kernel(Params p, RolloutArgs ra
             if (need) { reset_lane(p, g, s, rg, false, nullptr); ret0 = ret1 = 0; }
             gather(g, s);
             float o2[L];
-            observe<N>(s, o2);
+            observe<N>(p, s, o2);
             if (need) {
 #pragma unroll
                 for (int c = 0; c < L; ++c) o[c] = o2[c];
@@ -252,7 +256,7 @@ __global__ void __launch_bounds__(BLOCK) rollout_kernel(Params p, RolloutArgs ra
         }
         double rew;
         tick<N, CONT>(p, g, s, rg, adisc, a, spread_u, rew, ret0, ret1, tl);
-        observe<N>(s, o);
+        observe<N>(p, s, o);
         if (writer) {
             const long long ra_i = row * N + g.k;
             if (ra.rp.new_state) {
@@ -340,6 +344,48 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+// ---- observation tables (tick.cuh pair_obs) ------------------------------------------------------
+// One copy per device, shared by every handle on it and never freed (34.6 MB).  Evaluated on the host
+// with the host libm and one rounding per operation, i.e. exactly what CPython computes for
+// rel_angle / dist (battle_env.py:38-58) on this machine.
+struct ObsTables { double *t360 = nullptr; float *odt = nullptr; };
+static ObsTables g_tables[64];
+static std::mutex g_tables_mu;
+
+static int obs_tables_for(int device, ObsTables *out) {
+    std::lock_guard<std::mutex> lk(g_tables_mu);
+    if (device < 0 || device >= 64) return fail(BS_E_INVALID, "device index out of range");
+    ObsTables &tb = g_tables[device];
+    if (!tb.t360) {
+        std::vector<double> t((size_t)T_W * T_H);
+        std::vector<float> od((size_t)OD_W * OD_H);
+        const double two_pi = 2 * M_PI;                                   // 2*math.pi
+        const volatile double diag = std::sqrt(std::pow(1200.0, 2) + std::pow(800.0, 2));  // battle_env.py:230
+        for (int dy = -T_DY; dy <= T_DY; ++dy)
+            for (int dx = -T_DX; dx <= T_DX; ++dx) {
+                volatile double r = std::atan2((double)dy, (double)dx);  // battle_env.py:46
+                if (r < 0) r = r + two_pi;                                // rads %= 2*math.pi (float_rem)
+                volatile double degs = r * (180.0 / M_PI);               // math.degrees
+                t[(size_t)(dy + T_DY) * T_W + (dx + T_DX)] = 360 - degs;  // battle_env.py:49
+            }
+        for (int dy = 0; dy <= T_DY; ++dy)
+            for (int dx = 0; dx <= T_DX; ++dx) {
+                volatile double d = std::sqrt((double)(dx * dx + dy * dy));  // battle_env.py:58
+                volatile double a = d / diag;
+                volatile double b = a * 2;
+                od[(size_t)dy * OD_W + dx] = (float)(b - 1);                  // stored into a float32 array, :230
+            }
+        double *dt = nullptr; float *dd = nullptr;
+        CU(cudaMalloc(&dt, t.size() * sizeof(double)));
+        CU(cudaMalloc(&dd, od.size() * sizeof(float)));
+        CU(cudaMemcpy(dt, t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(dd, od.data(), od.size() * sizeof(float), cudaMemcpyHostToDevice));
+        tb.t360 = dt; tb.odt = dd;
+    }
+    *out = tb;
+    return BS_OK;
+}
+
 template <typename T>
 static int dalloc(bs_handle *h, T **ptr, size_t n) {
     void *q = nullptr;
@@ -424,6 +470,9 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
         bs_destroy(h);
         return rc;
     }
+    ObsTables tb;
+    if ((rc = obs_tables_for(device, &tb))) { bs_destroy(h); return rc; }
+    p.t360 = tb.t360; p.odt = tb.odt;
     // every env starts "done" (nothing spawned yet): the first reset / rollout tick spawns it
     std::vector<uint32_t> meta((size_t)n_envs, 1u << 16);
     CU(cudaMemcpy(p.meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));

@@ -55,7 +55,15 @@ struct Params {
     uint32_t *episode;    // [E]
     double *ret;          // [E*2]
     unsigned long long *counters;  // [8]
+    // Observation tables, built once per device by the host with the host libm -- the libm CPython's
+    // math module calls -- and kept resident in the 126 MB L2 (DESIGN.md "Observation tables").
+    const double *t360;   // [T_H][T_W]   360 - degrees(atan2(dy,dx) mod 2pi), battle_env.py:46-49
+    const float *odt;     // [OD_H][OD_W] float32(sqrt(dx^2+dy^2)/diag*2-1),   battle_env.py:54-58,230
 };
+
+// Table geometry: every pair of on-field points (sprites.py:9-10) has dx in [-1200,1200], dy in [-800,800].
+constexpr int T_DX = 1200, T_DY = 800, T_W = 2 * T_DX + 1, T_H = 2 * T_DY + 1;
+constexpr int OD_W = T_DX + 1, OD_H = T_DY + 1;
 
 // The block's bullet ring in shared memory: [slot][thread].
 struct Ring {
@@ -159,35 +167,41 @@ __device__ __forceinline__ void gather(const Geo<N> &g, Lane<N> &s) {
     }
 }
 
+// float32(rel / 360) for battle_env.py:231,242 without the double division: q = rel * (1/360) is
+// within 2 ulp of the quotient, so float(q) can differ from float(rel / 360) only when q lies within
+// a few double ulps of a float rounding midpoint (low 29 mantissa bits == 0x10000000); only then is
+// the division itself evaluated.  The result is the reference's float in every case.
+__device__ __forceinline__ float div360_f32(double rel) {
+    const double q = rel * (1.0 / 360.0);
+    const uint32_t low = (uint32_t)__double2loint(q) & 0x1fffffffu;
+    if (low - 0x0ffffffcu <= 8u) return (float)(rel / 360);
+    return (float)q;
+}
+
 // rel_angle / 360 -- battle_env.py:38-52,231 ; dist / diag * 2 - 1 -- battle_env.py:54-58,230.
-// One out-of-line copy per kernel (instruction-cache footprint); returns (od, oa).
-__device__ __noinline__ float2 pair_obs(int dx, int dy, double a0) {
-    double d = sqrt((double)(dx * dx + dy * dy));
-    float od = (float)(d / DIAG * 2 - 1);
-    double r = atan2((double)dy, (double)dx);
-    if (r < 0) r += TWO_PI;                    // Python float %: fmod plus sign fix-up
-    double degs = r * RAD2DEG;
-    double rel = 180 + a0 - (360 - degs);
+// atan2, the % 2pi, degrees() and the sqrt were evaluated by the host for every integer (dx, dy);
+// what is left is the part that depends on the observer's direction.  Returns (od, oa).
+__device__ __forceinline__ float2 pair_obs(const Params &p, int dx, int dy, double a0) {
+    const float od = __ldg(p.odt + abs(dy) * OD_W + abs(dx));
+    const double t = __ldg(p.t360 + (dy + T_DY) * T_W + (dx + T_DX));
+    double rel = 180 + a0 - t;
     if (rel < -180) rel += 360;
     if (rel > 180) rel -= 360;
-    return make_float2(od, (float)(rel / 360));
+    return make_float2(od, div360_f32(rel));
 }
 
 // observe -- battle_env.py:202-244, for the lane's own plane; needs a fresh gather().
 template <int N>
-__device__ __forceinline__ void observe(const Lane<N> &s, float (&o)[3 * N + 2]) {
+__device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float (&o)[3 * N + 2]) {
+    // every lane issues all its table loads (dead planes keep an on-field position); selects follow
+    const bool me = s.hp > 0;
+    float2 r = pair_obs(p, s.x - s.ebx, s.y - s.eby, s.dir);
+    o[0] = me ? r.x : -1.0f; o[1] = me ? r.y : -1.0f;
 #pragma unroll
-    for (int c = 0; c < 3 * N + 2; ++c) o[c] = -1.0f;
-    if (s.hp > 0) {
-        float2 r = pair_obs(s.x - s.ebx, s.y - s.eby, s.dir);
-        o[0] = r.x; o[1] = r.y;
-#pragma unroll
-        for (int j = 0; j < N; ++j) {
-            if ((s.am >> j) & 1u) {
-                r = pair_obs(s.x - (int)(s.exy[j] & 0xffffu), s.y - (int)(s.exy[j] >> 16), s.dir);
-                o[2 + 3 * j] = 1.0f; o[3 + 3 * j] = r.x; o[4 + 3 * j] = r.y;
-            }
-        }
+    for (int j = 0; j < N; ++j) {
+        r = pair_obs(p, s.x - (int)(s.exy[j] & 0xffffu), s.y - (int)(s.exy[j] >> 16), s.dir);
+        const bool seen = me && ((s.am >> j) & 1u);
+        o[2 + 3 * j] = seen ? 1.0f : -1.0f; o[3 + 3 * j] = seen ? r.x : -1.0f; o[4 + 3 * j] = seen ? r.y : -1.0f;
     }
 }
 
