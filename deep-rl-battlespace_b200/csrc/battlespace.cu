@@ -43,10 +43,10 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(Params p, const uint8_t *m
     Geo<N> g(global_warp(), p.E);
     Lane<N> s;
     double ret0, ret1;
-    load_lane(p, g, s, rg, ret0, ret1);
+    load_lane(p, g, s, &rg, ret0, ret1);
     const bool need = g.valid && (mask == nullptr || mask[g.e] != 0);
     if (need) {
-        reset_lane(p, g, s, rg, draws != nullptr, draws ? draws + g.e * (4 + 6 * N) : nullptr);
+        reset_lane(p, g, s, &rg, draws != nullptr, draws ? draws + g.e * (4 + 6 * N) : nullptr);
         ret0 = ret1 = 0;
     }
     gather(g, s);
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(Params p, const uint8_t *m
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
     }
-    if (need) store_lane(p, g, s, rg, ret0, ret1, true);
+    if (need) store_lane(p, g, s, &rg, ret0, ret1, true);
 }
 
 struct StepArgs {
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
     Geo<N> g(global_warp(), p.E);
     Lane<N> s;
     double ret0, ret1;
-    load_lane(p, g, s, rg, ret0, ret1);
+    load_lane(p, g, s, &rg, ret0, ret1);
 
     float o[L];
     const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT;  // kernel-uniform
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
             if (sa.winner) sa.winner[g.e] = (int8_t)s.winner;
         }
     }
-    store_lane(p, g, s, rg, ret0, ret1, false);
+    store_lane(p, g, s, &rg, ret0, ret1, false);
     flush_tally<N>(p, tl);
 }
 
@@ -199,11 +199,15 @@ struct RolloutArgs {
 template <int N, bool CONT>
 __global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Params p, RolloutArgs ra) {
     constexpr int L = 3 * N + 2, A = CONT ? 3 : 4;
-    __shared__ Ring rg;
+    __shared__ WarpPool pools[WARPS];
+    WarpPool &w = pools[threadIdx.x >> 5];
     Geo<N> g(global_warp(), p.E);
     Lane<N> s;
     double ret0, ret1;
-    load_lane(p, g, s, rg, ret0, ret1);
+    load_lane(p, g, s, nullptr, ret0, ret1);
+    int cnt;
+    pool_load<N>(p, g, s, w, cnt);
+    pool_publish_base<N>(g, s, w);
     gather(g, s);
     float o[L];
     observe<N>(p, s, o);
@@ -218,7 +222,7 @@ __global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Para
         // auto-reset: the game loop's env.reset() -- main.py:148
         const bool need = g.valid && s.env_done;
         if (__any_sync(FULL, need)) {
-            if (need) { reset_lane(p, g, s, rg, false, nullptr); ret0 = ret1 = 0; }
+            if (need) { reset_lane(p, g, s, nullptr, false, nullptr); ret0 = ret1 = 0; pool_publish_base<N>(g, s, w); }
             gather(g, s);
             float o2[L];
             observe<N>(p, s, o2);
@@ -246,16 +250,22 @@ __global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Para
                     for (int c = 0; c < 4; ++c) raw[c] = src[c];
                     adisc = argmax4(raw);
                 }
-                uint32_t w[4]; double u[5];
-                env_philox(p, g.e, s.episode, s.tick, g.i, PURPOSE_AGENT_TICK, w);
-                agent_tick_units(w, u);
+                uint32_t w4[4]; double u[5];
+                env_philox(p, g.e, s.episode, s.tick, g.i, PURPOSE_AGENT_TICK, w4);
+                agent_tick_units(w4, u);
                 spread_u = u[4];
             } else {
                 lane_policy<N, CONT>(p, g, s, pol, o, nullptr, adisc, a, spread_u, raw);
             }
         }
         double rew;
-        tick<N, CONT>(p, g, s, rg, adisc, a, spread_u, rew, ret0, ret1, tl);
+        {
+            TickCtx c;
+            tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, false, c);
+            unsigned ev; int died_ai;
+            bullets_dense<N>(g, s, w, cnt, c, need, ev, died_ai);
+            tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
+        }
         observe<N>(p, s, o);
         if (writer) {
             const long long ra_i = row * N + g.k;
@@ -274,7 +284,8 @@ __global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Para
         row += ra.e_mod;
         if (row >= ra.rp.capacity) row -= ra.rp.capacity;
     }
-    store_lane(p, g, s, rg, ret0, ret1, true);
+    store_lane(p, g, s, nullptr, ret0, ret1, true);
+    pool_store<N>(p, g, s, w, cnt);
     flush_tally<N>(p, tl);
 }
 

@@ -290,33 +290,37 @@ __device__ __forceinline__ unsigned plane_overlaps(const Lane<N> &s, uint32_t po
     return cm;
 }
 
-// One env tick -- parallel_env.step, battle_env.py:281-381.
+// ---- one env tick -- parallel_env.step, battle_env.py:281-381 -----------------------------------
+// The tick is split into three parts so that the single-tick kernels (bullets in a per-lane ring)
+// and the fused rollout (bullets in a dense per-warp pool) share everything but the bullet pass:
+//   tick_begin   preamble + actions of the alive planes; yields the spawn words of this lane
+//   bullets_*    move bullets, settle misses / base hits, resolve plane hits in list order
+//   tick_end     rewards in the reference's accumulation order, base damage, win / tie, report sums
+struct TickCtx {
+    bool active, run, tie_now, time_tie;
+    uint32_t spawnP;   // bullet pos word (0 = no spawn)
+    int32_t spawnD;    // sx + sy * 65536
+};
+
 //   adisc / a[3] : this lane's decoded action (clipped / argmax-ed);  spread_u : its Bullet draw.
-//   rew          : this lane's reward for the tick (double, reference accumulation order).
-// On return s holds the new state and gather() data is current (positions after the move,
-// enemy hp after the bullet loop), so observe() can be called directly.
 template <int N, bool CONT>
-__device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &s, Ring &rg, int adisc,
-                                     const double (&a)[3], double spread_u, double &rew,
-                                     double &ret0, double &ret1, Tally &tl, bool no_actions = false) {
-    const int tid = threadIdx.x;
-    rew = 0.0;
-    const bool active = g.valid && !s.env_done;                        // :303-306
-    const unsigned alive_b = __ballot_sync(FULL, active && s.hp > 0);
-    const bool any_alive = !no_actions && (alive_b & g.gmask()) != 0;  // len(actions) == 0 also ties
-    const bool tie_now = active && !any_alive;                         // :309-313
-    const bool adv = active && any_alive;
-    s.tick += adv ? 1 : 0;                                             // :316
-    const bool time_tie = adv && s.tick >= p.tie_tick;                 // :319-323
-    const bool run = adv && !time_tie;
-    if (run) s.head = s.head == SLOTS - 1 ? 0 : s.head + 1;
-    const int h = s.head;
+__device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lane<N> &s, int adisc,
+                                           const double (&a)[3], double spread_u, bool no_actions, TickCtx &c) {
+    c.active = g.valid && !s.env_done;                                  // :303-306
+    const unsigned alive_b = __ballot_sync(FULL, c.active && s.hp > 0);
+    const bool any_alive = !no_actions && (alive_b & g.gmask()) != 0;   // len(actions) == 0 also ties
+    c.tie_now = c.active && !any_alive;                                 // :309-313
+    const bool adv = c.active && any_alive;
+    s.tick += adv ? 1 : 0;                                              // :316
+    c.time_tie = adv && s.tick >= p.tie_tick;                           // :319-323
+    c.run = adv && !c.time_tie;
+    if (c.run) s.head = s.head == SLOTS - 1 ? 0 : s.head + 1;
 
     // ---- actions of the planes that are alive, :325-329 + process_action :383-424 -----------
     const int x0 = s.x, y0 = s.y;
     const double d0 = s.dir;
     bool shoot = false;
-    if (run && s.hp > 0) {
+    if (c.run && s.hp > 0) {
         double mdir = s.dir, speed = 215;
         bool move = true;
         if (CONT) {
@@ -334,65 +338,46 @@ __device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &
     // Bullet.__init__ -- sprites.py:293-318.  From here on the bullet is integer: its per-update
     // displacement d = 45*cos/sin is constant, and trunc(int + d) == int + floor(d) except that
     // a result in (-1,0) truncates to 0 (flagged "exact" when d itself is an integer).
-    if (run) {
-        uint32_t P = 0;
-        int32_t D = 0;
-        if (shoot) {
-            double2 cssn = cos_sin_dir(d0 + (spread_u * 8 - 4));
-            double ddx = (450 * 0.1) * cssn.x, ddy = (450 * 0.1) * cssn.y;
-            double fx = floor(ddx), fy = floor(ddy);
-            P = (((uint32_t)x0 | ((uint32_t)y0 << 16)) + B_BIAS) | B_VALID | (fx == ddx ? B_XEXACT : 0u) |
-                (fy == ddy ? B_YEXACT : 0u);
-            D = (int)fx + (int)fy * 65536;
-        }
-        rg.pos[h][tid] = P;
-        rg.dlt[h][tid] = D;
+    c.spawnP = 0; c.spawnD = 0;
+    if (shoot) {
+        double2 cssn = cos_sin_dir(d0 + (spread_u * 8 - 4));
+        double ddx = (450 * 0.1) * cssn.x, ddy = (450 * 0.1) * cssn.y;
+        double fx = floor(ddx), fy = floor(ddy);
+        c.spawnP = (((uint32_t)x0 | ((uint32_t)y0 << 16)) + B_BIAS) | B_VALID | (fx == ddx ? B_XEXACT : 0u) |
+                   (fy == ddy ? B_YEXACT : 0u);
+        c.spawnD = (int)fx + (int)fy * 65536;
     }
+}
 
-    gather(g, s);  // enemy positions after the move, hp before the bullet loop
+// One Bullet.update (sprites.py:321-351) up to the plane test, on the packed words.  `age` counts
+// the updates including this one.  Returns 1 = miss (range or off-screen, :334-341), 0 otherwise;
+// P is advanced (with the trunc-toward-zero corner: a coordinate of -1 that came from a sum in
+// (-1,0) is 0, the C cast in pygame's Rect setter).
+__device__ __forceinline__ bool bullet_advance(uint32_t &P, int32_t dlt, int age) {
+    P += (uint32_t)dlt;
+    uint32_t Q = (P & B_POS) - B_BIAS;  // fields x, y
+    bool miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
+    if (miss) {
+        if ((Q & 0xffffu) == 0xffffu && !(P & B_XEXACT)) { P += 1u; Q += 1u; }
+        if ((Q >> 16) == 0xffffu && !(P & B_YEXACT)) { P += 0x10000u; Q += 0x10000u; }
+        miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
+    }
+    return miss || age >= SLOTS;  // 12th update: dist_travelled >= 500, sprites.py:334-337
+}
 
-    // ---- bullets, oldest first; same age: agent order -- :332-360, sprites.py:321-351 --------
-    // Phase 1 (no ordering needed): move every bullet, settle misses and base hits, and flag the
-    // bullets that overlap an enemy plane alive at the start of the loop.  ev: 2 bits per age
-    // index a (0 = oldest): 1 miss, 2 base hit, 3 plane hit.
-    unsigned ev = 0, cand = 0;
-    int base_hits = 0;
-    const uint32_t baseT = (((uint32_t)(s.ebx - 33)) | ((uint32_t)(s.eby - 32) << 16)) + B_BIAS;
-    int slot = h + 1 == SLOTS ? 0 : h + 1;
-    if (run && (rg.pos[slot][tid] & B_VALID)) {  // 12th update: dist_travelled >= 500, sprites.py:334-337
-        ev = 1u;
-        rg.pos[slot][tid] = 0;
-    }
-#pragma unroll 1
-    for (int ai = 1; ai < SLOTS; ++ai) {
-        slot = slot + 1 == SLOTS ? 0 : slot + 1;
-        uint32_t P = rg.pos[slot][tid];
-        if (run && (P & B_VALID)) {
-            P += (uint32_t)rg.dlt[slot][tid];
-            uint32_t Q = (P & B_POS) - B_BIAS;  // fields x, y
-            bool miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
-            if (miss) {  // corner: a coordinate of -1 that came from a sum in (-1,0) is 0 (C cast)
-                if ((Q & 0xffffu) == 0xffffu && !(P & B_XEXACT)) { P += 1u; Q += 1u; }
-                if ((Q >> 16) == 0xffffu && !(P & B_YEXACT)) { P += 0x10000u; Q += 0x10000u; }
-                miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
-            }
-            if (miss) { ev |= 1u << (2 * ai); P = 0; }
-            else if (rect_hit((P & B_POS) - baseT, 67u, 64u)) { ev |= 2u << (2 * ai); base_hits += 1; P = 0; }
-            else if (plane_overlaps<N>(s, P) & s.am) cand |= 1u << ai;
-            rg.pos[slot][tid] = P;
-        }
-    }
-    // Phase 2 (ordered, only for ages where some lane of the warp has a candidate): resolve the N
-    // same-age bullets of each team in agent order; a plane that dies is invisible to later ones.
-    int died_ai = -1;
+// Phase 2 of the bullet loop (ordered; only for ages where some lane of the warp has a candidate):
+// resolve the N same-age bullets of each team in agent order; a plane that dies is invisible to
+// later ones (battle_env.py:348-360).  cm_of(ai) = this lane's overlap mask for its bullet of age
+// index ai; drop(ai) removes that bullet.  Updates ev (code 3 = plane hit), s.hp, s.ehp4, s.am.
+template <int N, class CmOf, class Drop>
+__device__ __forceinline__ void resolve_plane_hits(const Geo<N> &g, Lane<N> &s, unsigned cand, unsigned &ev,
+                                                   int &died_ai, CmOf cm_of, Drop drop) {
     unsigned allc = __reduce_or_sync(FULL, cand);
     while (allc) {
         const int ai = __ffs(allc) - 1;
         allc &= allc - 1;
-        int sl = h + 1 + ai;
-        if (sl >= SLOTS) sl -= SLOTS;
         unsigned cm = 0;
-        if ((cand >> ai) & 1u) cm = plane_overlaps<N>(s, rg.pos[sl][tid]);
+        if ((cand >> ai) & 1u) cm = cm_of(ai);
         int victim = -1;
 #pragma unroll 1
         for (int kk = 0; kk < N; ++kk) {
@@ -410,8 +395,185 @@ __device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &
                 if (s.hp <= 0 && died_ai < 0) died_ai = ai;
             }
         }
-        if (victim >= 0) { ev |= 3u << (2 * ai); rg.pos[sl][tid] = 0; }
+        if (victim >= 0) { ev |= 3u << (2 * ai); drop(ai); }
     }
+}
+
+// Bullets in the per-lane ring -- :332-360, sprites.py:321-351.  Oldest first; same age: agent order.
+// Phase 1 (no ordering needed): move every bullet, settle misses and base hits, and flag the
+// bullets that overlap an enemy plane alive at the start of the loop.  ev: 2 bits per age
+// index ai (0 = oldest): 1 miss, 2 base hit, 3 plane hit.
+template <int N>
+__device__ __forceinline__ void bullets_ring(const Geo<N> &g, Lane<N> &s, Ring &rg, const TickCtx &c,
+                                             unsigned &ev, int &died_ai) {
+    const int tid = threadIdx.x;
+    const int h = s.head;
+    const bool run = c.run;
+    if (run) { rg.pos[h][tid] = c.spawnP; rg.dlt[h][tid] = c.spawnD; }
+    gather(g, s);  // enemy positions after the move, hp before the bullet loop
+    unsigned cand = 0;
+    ev = 0; died_ai = -1;
+    const uint32_t baseT = (((uint32_t)(s.ebx - 33)) | ((uint32_t)(s.eby - 32) << 16)) + B_BIAS;
+    int slot = h;
+#pragma unroll 1
+    for (int ai = 0; ai < SLOTS; ++ai) {
+        slot = slot + 1 == SLOTS ? 0 : slot + 1;
+        uint32_t P = rg.pos[slot][tid];
+        if (run && (P & B_VALID)) {
+            if (bullet_advance(P, rg.dlt[slot][tid], SLOTS - ai)) { ev |= 1u << (2 * ai); P = 0; }
+            else if (rect_hit((P & B_POS) - baseT, 67u, 64u)) { ev |= 2u << (2 * ai); P = 0; }
+            else if (plane_overlaps<N>(s, P) & s.am) cand |= 1u << ai;
+            rg.pos[slot][tid] = P;
+        }
+    }
+    resolve_plane_hits<N>(g, s, cand, ev, died_ai,
+        [&](int ai) { int sl = h + 1 + ai; if (sl >= SLOTS) sl -= SLOTS; return plane_overlaps<N>(s, rg.pos[sl][tid]); },
+        [&](int ai) { int sl = h + 1 + ai; if (sl >= SLOTS) sl -= SLOTS; rg.pos[sl][tid] = 0; });
+}
+
+// ---- bullets in a dense per-warp pool (fused rollout) ---------------------------------------------
+// In the ring only ~1/4 of the slots hold a bullet, so a lane-per-owner loop over 12 slots runs at
+// ~8 of 32 lanes (profiles/r1c_*).  The rollout kernel therefore keeps the warp's live bullets
+// packed in shared memory, any lane updates any bullet, and results travel back to the owner lane
+// as bits keyed by (owner, age) -- which is all the ordered part of the loop needs.
+//   pos  : as in the ring (0 = dead entry, squeezed out by the next pass)
+//   meta : (sx + sy*65536) in bits 0..22 (two's complement) | owner lane << 23 | updates done << 28
+constexpr int WARPS = BLOCK / 32;
+constexpr int POOL_CAP = 32 * SLOTS;  // <= 11 survivors + 1 spawn per lane at the start of a pass
+struct WarpPool {
+    uint32_t pos[POOL_CAP], meta[POOL_CAP];
+    uint32_t ev[32], cand[32];   // per owner lane: event codes / candidate ages of this tick
+    uint32_t candt[SLOTS][32];   // per (age index, owner): pool index << 8 | overlap mask
+    uint32_t plane[32];          // x | y << 16 | hp << 28 of every lane's plane (after the move)
+    uint32_t baseT[32];          // enemy-base test word | first lane of the enemy team << 27
+};
+
+__device__ __forceinline__ uint32_t pack_meta(int32_t dlt, int owner, int age) {
+    return ((uint32_t)dlt & 0x7fffffu) | ((uint32_t)owner << 23) | ((uint32_t)age << 28);
+}
+__device__ __forceinline__ int32_t meta_dlt(uint32_t m) { return (int32_t)(m << 9) >> 9; }
+
+template <int N>
+__device__ __forceinline__ void pool_publish_base(const Geo<N> &g, const Lane<N> &s, WarpPool &w) {
+    w.baseT[g.lane] = ((((uint32_t)(s.ebx - 33)) | ((uint32_t)(s.eby - 32) << 16)) + B_BIAS) | ((uint32_t)g.eb << 27);
+}
+
+// kill: this lane's env was reset at the top of this tick (its old bullets vanish, battle_env.py:272).
+template <int N>
+__device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpPool &w, int &cnt, const TickCtx &c,
+                                              bool kill, unsigned &ev, int &died_ai) {
+    const int lane = g.lane;
+    const unsigned lt = (1u << lane) - 1u;
+    w.plane[lane] = (uint32_t)s.x | ((uint32_t)s.y << 16) | ((uint32_t)(s.hp > 0 ? s.hp : 0) << 28);
+    const unsigned runmask = __ballot_sync(FULL, c.run), killmask = __ballot_sync(FULL, kill);
+    const unsigned sp = __ballot_sync(FULL, c.spawnP != 0);
+    if (c.spawnP) {
+        const int idx = cnt + __popc(sp & lt);
+        w.pos[idx] = c.spawnP;
+        w.meta[idx] = pack_meta(c.spawnD, lane, 0);
+    }
+    const int cnt_in = cnt + __popc(sp);
+    __syncwarp();
+    gather(g, s);  // enemy positions after the move, hp before the bullet loop
+    int out = 0;
+#pragma unroll 1
+    for (int base = 0; base < cnt_in; base += 32) {
+        const int idx = base + lane;
+        uint32_t P = 0, M = 0;
+        if (idx < cnt_in) { P = w.pos[idx]; M = w.meta[idx]; }
+        const int owner = (M >> 23) & 31;
+        int age = M >> 28;
+        bool keep = (P & B_VALID) != 0;
+        unsigned cm = 0;
+        int ai = 0;
+        if (keep && ((killmask >> owner) & 1u) && age >= 1) keep = false;
+        else if (keep && ((runmask >> owner) & 1u)) {
+            ai = SLOTS - 1 - age;
+            age += 1;
+            const uint32_t bt = w.baseT[owner];
+            if (bullet_advance(P, meta_dlt(M), age)) { atomicOr(&w.ev[owner], 1u << (2 * ai)); keep = false; }
+            else if (rect_hit((P & B_POS) - (bt & 0x07ffffffu), 67u, 64u)) { atomicOr(&w.ev[owner], 2u << (2 * ai)); keep = false; }
+            else {
+                const uint32_t Pp = (P & B_POS) - PLANE_OFF;
+                const int eb = bt >> 27;
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    const uint32_t e = w.plane[eb + j];
+                    cm |= ((e >> 28) != 0 && rect_hit(Pp - (e & 0x03ff07ffu), 55u, 50u) ? 1u : 0u) << j;
+                }
+                M = (M & 0x0fffffffu) | ((uint32_t)age << 28);
+            }
+        }
+        const unsigned kb = __ballot_sync(FULL, keep);
+        const int nidx = out + __popc(kb & lt);
+        if (keep) {
+            w.pos[nidx] = P; w.meta[nidx] = M;
+            if (cm) { atomicOr(&w.cand[owner], 1u << ai); w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm; }
+        }
+        out += __popc(kb);
+    }
+    cnt = out;
+    __syncwarp();
+    ev = w.ev[lane];
+    const unsigned cand = w.cand[lane];
+    w.ev[lane] = 0; w.cand[lane] = 0;
+    died_ai = -1;
+    resolve_plane_hits<N>(g, s, cand, ev, died_ai,
+        [&](int ai) { return w.candt[ai][lane] & 0xffu; },
+        [&](int ai) { w.pos[w.candt[ai][lane] >> 8] = 0; });
+}
+
+// ring (HBM state format) -> pool at the start of a launch: oldest age first
+template <int N>
+__device__ __forceinline__ void pool_load(const Params &p, const Geo<N> &g, const Lane<N> &s, WarpPool &w, int &cnt) {
+    const int lane = g.lane;
+    const unsigned lt = (1u << lane) - 1u;
+    const long long a = g.e * (2 * N) + g.i, EP = p.E * (2 * N);
+    cnt = 0;
+    w.ev[lane] = 0; w.cand[lane] = 0;
+#pragma unroll 1
+    for (int o = SLOTS - 2; o >= 0; --o) {  // exported index o = updates done - 1 (bs_get_state)
+        int q = s.head - o; if (q < 0) q += SLOTS;
+        uint32_t P = 0; int32_t D = 0;
+        if (g.valid) { P = p.bul_pos[q * EP + a]; D = p.bul_dlt[q * EP + a]; }
+        const bool v = (P & B_VALID) != 0;
+        const unsigned b = __ballot_sync(FULL, v);
+        if (v) { const int idx = cnt + __popc(b & lt); w.pos[idx] = P; w.meta[idx] = pack_meta(D, lane, o + 1); }
+        cnt += __popc(b);
+    }
+    __syncwarp();
+}
+
+// pool -> ring at the end of a launch
+template <int N>
+__device__ __forceinline__ void pool_store(const Params &p, const Geo<N> &g, const Lane<N> &s, WarpPool &w, int cnt) {
+    const int lane = g.lane;
+    const long long EP = p.E * (2 * N);
+    const long long a0 = (g.e * (2 * N) + g.i) - lane;  // agent index of lane 0 (lanes map to consecutive agents)
+    if (g.valid) {
+#pragma unroll
+        for (int q = 0; q < SLOTS; ++q) { p.bul_pos[q * EP + a0 + lane] = 0; p.bul_dlt[q * EP + a0 + lane] = 0; }
+    }
+    w.ev[lane] = (uint32_t)s.head;
+    __syncwarp();
+    const long long a00 = __shfl_sync(FULL, a0, 0);  // lane 0 is always a valid lane of a launched warp
+#pragma unroll 1
+    for (int idx = lane; idx < cnt; idx += 32) {
+        const uint32_t P = w.pos[idx], M = w.meta[idx];
+        if (P & B_VALID) {
+            const int owner = (M >> 23) & 31, age = M >> 28;
+            int q = (int)w.ev[owner] - (age - 1); if (q < 0) q += SLOTS;
+            p.bul_pos[q * EP + a00 + owner] = P;
+            p.bul_dlt[q * EP + a00 + owner] = meta_dlt(M);
+        }
+    }
+}
+
+//   rew : this lane's reward for the tick (double, reference accumulation order).
+template <int N>
+__device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<N> &s, const TickCtx &c, unsigned ev,
+                                         int died_ai, double &rew, double &ret0, double &ret1, Tally &tl) {
+    rew = 0.0;
     // Rewards in the reference's accumulation order (:337-360): per age, own bullet outcome; a
     // victim's die_punishment precedes its own same-age outcome for blue (red bullets come first
     // in the list) and follows it for red.
@@ -428,7 +590,8 @@ __device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &
             }
         }
     }
-    // base damage: no alive check, hp may go negative
+    // base damage: no alive check, hp may go negative.  code 2 = high bit only.
+    const int base_hits = __popc((ev >> 1) & ~ev & 0x00555555u);
     int mine_total = 0, foe_total = 0;
 #pragma unroll
     for (int kk = 0; kk < N; ++kk) {
@@ -439,11 +602,11 @@ __device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &
     s.bhp_own -= foe_total;
 
     // ---- win / tie -- :363-372, 469-496 -------------------------------------------------------
-    const bool i_won = run && s.bhp_enemy <= 0;  // the winners' planes get lose_punishment (sic)
-    const bool foe_won = run && s.bhp_own <= 0;
+    const bool i_won = c.run && s.bhp_enemy <= 0;  // the winners' planes get lose_punishment (sic)
+    const bool foe_won = c.run && s.bhp_own <= 0;
     if (i_won) rew += p.r_lose;
     const bool red_won = g.team == 0 ? i_won : foe_won, blue_won = g.team == 0 ? foe_won : i_won;
-    const bool tie = tie_now || time_tie;
+    const bool tie = c.tie_now || c.time_tie;
     if (red_won) s.winner = W_RED;
     if (blue_won) s.winner = W_BLUE;  // both bases dead: ends as 'blue', two games counted
     if (tie) s.winner = W_TIE;
@@ -456,7 +619,7 @@ __device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &
         r0 += __shfl_sync(FULL, rew, g.gb + kk);
         r1 += __shfl_sync(FULL, rew, g.gb + N + kk);
     }
-    if (active && g.i == 0) {
+    if (c.active && g.i == 0) {
         ret0 += r0; ret1 += r1;
         tl.ticks += 1;
         tl.wins_red += red_won; tl.wins_blue += blue_won; tl.ties += tie;
@@ -468,10 +631,23 @@ __device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &
     }
 }
 
+// The single-tick form used by step_kernel.  On return s holds the new state and gather() data is
+// current (positions after the move, enemy hp after the bullet loop), so observe() can follow.
+template <int N, bool CONT>
+__device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &s, Ring &rg, int adisc,
+                                     const double (&a)[3], double spread_u, double &rew,
+                                     double &ret0, double &ret1, Tally &tl, bool no_actions = false) {
+    TickCtx c;
+    tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, no_actions, c);
+    unsigned ev; int died_ai;
+    bullets_ring<N>(g, s, rg, c, ev, died_ai);
+    tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
+}
+
 // parallel_env.reset for one lane -- battle_env.py:246-279, sprites.py:74-91,238-252.
 // d_* are this lane's spawn values when injected (inj=true), else Philox.
 template <int N>
-__device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lane<N> &s, Ring &rg, bool inj,
+__device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lane<N> &s, Ring *rg, bool inj,
                                            const int32_t *draws /* this env's [4+6N] or null */) {
     s.episode += 1;
     int rbx, rby, bbx, bby, px, py, pd;
@@ -492,14 +668,16 @@ __device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lan
     s.x = px; s.y = py; s.dir = (double)pd; s.hp = 4;                               // battle_env.py:92
     s.ebx = g.team == 0 ? bbx : rbx; s.eby = g.team == 0 ? bby : rby;
     s.bhp_own = s.bhp_enemy = 5 * N;                                                // battle_env.py:91
+    if (rg) {
 #pragma unroll
-    for (int q = 0; q < SLOTS; ++q) rg.pos[q][threadIdx.x] = 0;
+        for (int q = 0; q < SLOTS; ++q) rg->pos[q][threadIdx.x] = 0;
+    }
     s.tick = 0; s.head = 0; s.env_done = 0; s.winner = W_NONE;
 }
 
 // ---- state <-> registers / shared ring --------------------------------------------------------
 template <int N>
-__device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane<N> &s, Ring &rg, double &ret0,
+__device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane<N> &s, Ring *rg, double &ret0,
                                           double &ret1) {
     constexpr int P = 2 * N;
     const int tid = threadIdx.x;
@@ -507,10 +685,12 @@ __device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane
     s.tick = 0; s.head = 0; s.env_done = 1; s.winner = 0; s.episode = 0; ret0 = ret1 = 0;
     if (g.valid) {
         const long long a = g.e * P + g.i, EP = p.E * P;
+        if (rg) {
 #pragma unroll
-        for (int q = 0; q < SLOTS; ++q) {
-            rg.pos[q][tid] = p.bul_pos[q * EP + a];
-            rg.dlt[q][tid] = p.bul_dlt[q * EP + a];
+            for (int q = 0; q < SLOTS; ++q) {
+                rg->pos[q][tid] = p.bul_pos[q * EP + a];
+                rg->dlt[q][tid] = p.bul_dlt[q * EP + a];
+            }
         }
         uint32_t pos = p.plane_pos[a];
         s.x = pos & 0xffff; s.y = pos >> 16;
@@ -524,14 +704,14 @@ __device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane
         s.tick = m & 0xfff; s.head = (m >> 12) & 0xf; s.env_done = (m >> 16) & 0xff; s.winner = (m >> 24) & 0xff;
         s.episode = p.episode[g.e];
         if (g.i == 0) { ret0 = p.ret[g.e * 2]; ret1 = p.ret[g.e * 2 + 1]; }
-    } else {
+    } else if (rg) {
 #pragma unroll
-        for (int q = 0; q < SLOTS; ++q) { rg.pos[q][tid] = 0; rg.dlt[q][tid] = 0; }
+        for (int q = 0; q < SLOTS; ++q) { rg->pos[q][tid] = 0; rg->dlt[q][tid] = 0; }
     }
 }
 
 template <int N>
-__device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, const Lane<N> &s, const Ring &rg,
+__device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, const Lane<N> &s, const Ring *rg,
                                            double ret0, double ret1, bool base_pos_too) {
     constexpr int P = 2 * N;
     if (!g.valid) return;
@@ -540,10 +720,12 @@ __device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, con
     p.plane_pos[a] = (uint32_t)s.x | ((uint32_t)s.y << 16);
     p.plane_dir[a] = s.dir;
     p.plane_hp[a] = (int8_t)s.hp;
+    if (rg) {
 #pragma unroll
-    for (int q = 0; q < SLOTS; ++q) {
-        p.bul_pos[q * EP + a] = rg.pos[q][tid];
-        p.bul_dlt[q * EP + a] = rg.dlt[q][tid];
+        for (int q = 0; q < SLOTS; ++q) {
+            p.bul_pos[q * EP + a] = rg->pos[q][tid];
+            p.bul_dlt[q * EP + a] = rg->dlt[q][tid];
+        }
     }
     if (g.k == 0) {  // first lane of each team owns its enemy's base record
         p.base_hp[g.e * 2 + (1 - g.team)] = (int16_t)s.bhp_enemy;
