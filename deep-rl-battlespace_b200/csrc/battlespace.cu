@@ -11,6 +11,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -258,6 +259,11 @@ __global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Para
                 lane_policy<N, CONT>(p, g, s, pol, o, nullptr, adisc, a, spread_u, raw);
             }
         }
+        if (writer && ra.rp.action) {  // the action row is complete before the tick: write it now
+            float *dst = ra.rp.action + (row * N + g.k) * A;
+#pragma unroll
+            for (int c = 0; c < A; ++c) dst[c] = raw[c];
+        }
         double rew;
         {
             TickCtx c;
@@ -273,10 +279,6 @@ __global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Para
                 float *dst = ra.rp.new_state + ra_i * L;
 #pragma unroll
                 for (int c = 0; c < L; ++c) dst[c] = o[c];
-            }
-            if (ra.rp.action) {
-#pragma unroll
-                for (int c = 0; c < A; ++c) ra.rp.action[ra_i * A + c] = raw[c];
             }
             if (ra.rp.reward) ra.rp.reward[ra_i] = (float)rew;
             if (ra.rp.done) ra.rp.done[ra_i] = (uint8_t)(s.env_done || s.hp <= 0);
@@ -335,6 +337,8 @@ static int fail(int code, const std::string &msg) { g_err = msg; return code; }
             return fail(BS_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));            \
     } while (0)
 
+struct ObsTables { double *t360 = nullptr; float *odt = nullptr; size_t bytes = 0; bool persist = false; };
+
 struct bs_handle {
     bs_config cfg;
     int N, P, L, A;
@@ -342,6 +346,7 @@ struct bs_handle {
     int64_t E;
     int device;
     Params p;
+    ObsTables tables;
     std::vector<void *> allocs;
     cudaStream_t hstream = nullptr;  // used by the *_host entry points
     // device staging for *_host calls (grown on demand)
@@ -359,7 +364,6 @@ struct DeviceGuard {
 // One copy per device, shared by every handle on it and never freed (34.6 MB).  Evaluated on the host
 // with the host libm and one rounding per operation, i.e. exactly what CPython computes for
 // rel_angle / dist (battle_env.py:38-58) on this machine.
-struct ObsTables { double *t360 = nullptr; float *odt = nullptr; };
 static ObsTables g_tables[64];
 static std::mutex g_tables_mu;
 
@@ -386,11 +390,22 @@ static int obs_tables_for(int device, ObsTables *out) {
                 volatile double b = a * 2;
                 od[(size_t)dy * OD_W + dx] = (float)(b - 1);                  // stored into a float32 array, :230
             }
-        double *dt = nullptr; float *dd = nullptr;
-        CU(cudaMalloc(&dt, t.size() * sizeof(double)));
-        CU(cudaMalloc(&dd, od.size() * sizeof(float)));
-        CU(cudaMemcpy(dt, t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice));
-        CU(cudaMemcpy(dd, od.data(), od.size() * sizeof(float), cudaMemcpyHostToDevice));
+        // one allocation, so that a single access-policy window covers both tables
+        const size_t tbytes = t.size() * sizeof(double), obytes = od.size() * sizeof(float);
+        char *blk = nullptr;
+        CU(cudaMalloc(&blk, tbytes + obytes));
+        double *dt = (double *)blk; float *dd = (float *)(blk + tbytes);
+        CU(cudaMemcpy(dt, t.data(), tbytes, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(dd, od.data(), obytes, cudaMemcpyHostToDevice));
+        tb.bytes = tbytes + obytes;
+        // Pin the tables in L2: set aside enough persisting L2 for them (B200: 126 MB L2).
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, device));
+        if (!getenv("BS_NO_L2_PERSIST") && (size_t)prop.persistingL2CacheMaxSize >= tb.bytes &&
+            (size_t)prop.accessPolicyMaxWindowSize >= tb.bytes &&
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, tb.bytes + (4u << 20)) == cudaSuccess)
+            tb.persist = true;
+        cudaGetLastError();
         tb.t360 = dt; tb.odt = dd;
     }
     *out = tb;
@@ -422,6 +437,25 @@ static int tie_tick_for(int n_agents) {  // battle_env.py:316-319: total_time ac
     volatile double t = 0;
     int k = 0;
     for (;;) { ++k; t = t + 0.1; if (t >= 10 + 2 * n_agents) return k; }
+}
+
+// Kernel launch with the observation tables marked persisting in L2 for this launch only (the
+// caller's stream is not modified).
+template <class... KArgs, class... Args>
+static cudaError_t launch(const bs_handle *h, void (*kern)(KArgs...), int grid, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(BLOCK); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    if (h->tables.persist) {
+        attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[0].val.accessPolicyWindow.base_ptr = (void *)h->tables.t360;
+        attr[0].val.accessPolicyWindow.num_bytes = h->tables.bytes;
+        attr[0].val.accessPolicyWindow.hitRatio = 1.0f;
+        attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+    }
+    return cudaLaunchKernelEx(&cfg, kern, args...);
 }
 
 static inline int grid_for_envs(int64_t E, int N) {
@@ -483,7 +517,7 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     }
     ObsTables tb;
     if ((rc = obs_tables_for(device, &tb))) { bs_destroy(h); return rc; }
-    p.t360 = tb.t360; p.odt = tb.odt;
+    p.t360 = tb.t360; p.odt = tb.odt; h->tables = tb;
     // every env starts "done" (nothing spawned yet): the first reset / rollout tick spawns it
     std::vector<uint32_t> meta((size_t)n_envs, 1u << 16);
     CU(cudaMemcpy(p.meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
@@ -515,9 +549,8 @@ int bs_reset(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float 
 
 static int launch_step(bs_handle *h, const StepArgs &sa, cudaStream_t st) {
     const int grid = grid_for_envs(h->E, h->N);
-    if (h->cont) { DISPATCH_N(h->N, step_kernel<N_, true><<<grid, BLOCK, 0, st>>>(h->p, sa)); }
-    else { DISPATCH_N(h->N, step_kernel<N_, false><<<grid, BLOCK, 0, st>>>(h->p, sa)); }
-    CU(cudaGetLastError());
+    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true>, grid, st, h->p, sa))); }
+    else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false>, grid, st, h->p, sa))); }
     return BS_OK;
 }
 
@@ -589,9 +622,8 @@ int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int 
     }
     cudaStream_t st = (cudaStream_t)stream;
     const int grid = grid_for_envs(h->E, h->N);
-    if (h->cont) { DISPATCH_N(h->N, rollout_kernel<N_, true><<<grid, BLOCK, 0, st>>>(h->p, ra)); }
-    else { DISPATCH_N(h->N, rollout_kernel<N_, false><<<grid, BLOCK, 0, st>>>(h->p, ra)); }
-    CU(cudaGetLastError());
+    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, rollout_kernel<N_, true>, grid, st, h->p, ra))); }
+    else { DISPATCH_N(h->N, CU(launch(h, rollout_kernel<N_, false>, grid, st, h->p, ra))); }
     return BS_OK;
 }
 

@@ -266,11 +266,17 @@ __device__ __forceinline__ double plane_rotate(double dir, double a) {
     return dir;
 }
 
-// Per-lane event counters accumulated over a launch (only the env's first lane counts).
+// Report counters.  Game ends are rare (once per ~150 ticks per env), so they go straight to the
+// global counters, warp-aggregated, when they happen; only the tick count lives in a register.
 struct Tally {
-    int wins_red = 0, wins_blue = 0, ties = 0, games = 0, ticks = 0;
-    long long ret_red = 0, ret_blue = 0;
+    int ticks = 0;
 };
+
+__device__ __forceinline__ long long warp_sum(long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
 
 // Packed rect test.  D = (bullet fields) - (target fields): both 16-bit fields must land in
 // [0, rx) x [0, ry).  A negative low field borrows from the high one, but then the low test has
@@ -619,14 +625,21 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
         r0 += __shfl_sync(FULL, rew, g.gb + kk);
         r1 += __shfl_sync(FULL, rew, g.gb + N + kk);
     }
-    if (c.active && g.i == 0) {
-        ret0 += r0; ret1 += r1;
-        tl.ticks += 1;
-        tl.wins_red += red_won; tl.wins_blue += blue_won; tl.ties += tie;
-        tl.games += (int)red_won + (int)blue_won + (int)tie;
-        if (s.env_done) {
-            tl.ret_red += __double2ll_rn(ret0 * 1048576.0);
-            tl.ret_blue += __double2ll_rn(ret1 * 1048576.0);
+    const bool first = c.active && g.i == 0;
+    if (first) { ret0 += r0; ret1 += r1; tl.ticks += 1; }
+    const bool ended = first && s.env_done;
+    if (__any_sync(FULL, ended)) {
+        const int nr = __popc(__ballot_sync(FULL, ended && red_won)), nb = __popc(__ballot_sync(FULL, ended && blue_won));
+        const int nt = __popc(__ballot_sync(FULL, ended && tie));
+        const long long sr = warp_sum(ended ? __double2ll_rn(ret0 * 1048576.0) : 0ll);
+        const long long sb = warp_sum(ended ? __double2ll_rn(ret1 * 1048576.0) : 0ll);
+        if (g.lane == 0) {
+            if (nr) atomicAdd(p.counters + C_WINS_RED, (unsigned long long)nr);
+            if (nb) atomicAdd(p.counters + C_WINS_BLUE, (unsigned long long)nb);
+            if (nt) atomicAdd(p.counters + C_TIES, (unsigned long long)nt);
+            atomicAdd(p.counters + C_GAMES, (unsigned long long)(nr + nb + nt));
+            atomicAdd(p.counters + C_RET_RED, (unsigned long long)sr);
+            atomicAdd(p.counters + C_RET_BLUE, (unsigned long long)sb);
         }
     }
 }
@@ -738,21 +751,13 @@ __device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, con
     }
 }
 
-// Launch-level counter flush: warp-reduce the per-lane tallies, one atomic per warp per counter.
-__device__ __forceinline__ long long warp_sum(long long v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
-    return v;
-}
-
+// Launch-level flush of the tick counters: one atomic per warp per counter.
 template <int N>
 __device__ __forceinline__ void flush_tally(const Params &p, const Tally &tl) {
-    long long v[8] = {tl.wins_red, tl.wins_blue, tl.ties, tl.games, tl.ret_red, tl.ret_blue,
-                      tl.ticks, (long long)tl.ticks * (2 * N)};
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        long long t = warp_sum(v[c]);
-        if ((threadIdx.x & 31) == 0 && t != 0) atomicAdd(p.counters + c, (unsigned long long)t);
+    const long long t = warp_sum((long long)tl.ticks);
+    if ((threadIdx.x & 31) == 0 && t != 0) {
+        atomicAdd(p.counters + C_TICKS, (unsigned long long)t);
+        atomicAdd(p.counters + C_AGENT_STEPS, (unsigned long long)(t * (2 * N)));
     }
 }
 
