@@ -106,18 +106,33 @@ def cpu_port_rate(steps, warmup, envs, threads=None):
     return steps * T_TICKS * envs * 2 * N_AGENTS / dt, dt, cores
 
 
+def calibrated_cpu_rate(steps, warmup, target_s):
+    """Size the env sample so that `steps` steps take about target_s seconds on this box's cores
+    (capped at the full 65,536-env workload), then time it."""
+    r0, _, _ = cpu_port_rate(1, 1, 2048)
+    envs = int(target_s * r0 / (max(steps, 1) * T_TICKS * 2 * N_AGENTS))
+    envs = max(2048, min(ENVS_PER_GPU, envs // 256 * 256))
+    rate, dt, cores = cpu_port_rate(steps, warmup, envs)
+    return rate, dt, cores, envs
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
-    envs = args.ref_envs
-    rate, dt, cores = cpu_port_rate(args.steps, args.warmup, envs)
-    sample = f"{envs} envs x {T_TICKS} ticks per step, {args.steps} steps ({dt:.1f} s), OpenMP over envs"
+    if args.ref_envs:
+        envs = args.ref_envs
+        rate, dt, cores = cpu_port_rate(args.steps, args.warmup, envs)
+    else:
+        rate, dt, cores, envs = calibrated_cpu_rate(args.steps, args.warmup, 20.0)
+    sample = (f"{envs} of 65536 envs x {T_TICKS} ticks per step, {args.steps} steps ({dt:.1f} s), "
+              f"OpenMP over envs on {cores} threads")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "3v3 continuous, red=uniform random, blue=instinct, fused 32-tick rollout + replay rows "
-                               "(CPU port of the reference tick; the Python reference tree is absent on this box)",
+        "config": {"workload": "BASELINE configs[2]: 3v3 continuous, red=uniform random, blue=instinct, fused 32-tick "
+                               "rollout + replay rows (C port of the reference tick; the reference is pure Python "
+                               "and its tree is absent on this box)",
                    "envs": envs, "ticks_per_step": T_TICKS},
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -131,7 +146,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=ENVS_PER_GPU, help="envs per GPU")
-    ap.add_argument("--ref-envs", type=int, default=2048, help="envs per step of the CPU arm")
+    ap.add_argument("--ref-envs", type=int, default=0, help="envs per step of the CPU arm (0: sized for ~20 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -214,9 +229,10 @@ def main():
             traffic = json.load(open(tp)).get("rollout_kernel_dram_bytes_per_launch")
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            rate, dt, cores = cpu_port_rate(6, 2, 2048)
+            rate, dt, cores, cenvs = calibrated_cpu_rate(10, 1, 12.0)
             cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": f"2048 envs x {T} ticks x 6 steps ({dt:.1f} s) of the same workload, OpenMP over envs"}
+                   "sample": f"{cenvs} of {E} envs x {T} ticks x 10 steps ({dt:.1f} s) of the same workload, "
+                             f"OpenMP over envs on {cores} threads"}
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

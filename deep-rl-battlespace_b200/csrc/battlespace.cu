@@ -270,9 +270,11 @@ __global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Para
             tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, false, c);
             unsigned ev; int died_ai;
             bullets_dense<N>(g, s, w, cnt, c, need, ev, died_ai);
+            ObsLoads<N> q;
+            observe_issue<N>(p, s, q);  // positions are final; hp / alive masks are settled by then
             tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
+            observe_finish<N>(s, q, o);
         }
-        observe<N>(p, s, o);
         if (writer) {
             const long long ra_i = row * N + g.k;
             if (ra.rp.new_state) {
@@ -714,6 +716,13 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), bp(EP * SLOTS);
     std::vector<int32_t> bd(EP * SLOTS);
     std::vector<int8_t> hp(EP);
+    // the observation tables (and the packed 11/10-bit plane words) cover on-field points only
+    for (size_t a = 0; a < EP; ++a)
+        if (v->plane_x[a] < 0 || v->plane_x[a] > 1200 || v->plane_y[a] < 0 || v->plane_y[a] > 800)
+            return fail(BS_E_INVALID, "bs_set_state: plane position outside the 1200x800 field");
+    for (size_t q = 0; q < (size_t)E * 2; ++q)
+        if (v->base_pos[q * 2] < 0 || v->base_pos[q * 2] > 1200 || v->base_pos[q * 2 + 1] < 0 || v->base_pos[q * 2 + 1] > 800)
+            return fail(BS_E_INVALID, "bs_set_state: base position outside the 1200x800 field");
     // age -> ring slot with head = tick mod 12 (any head works as long as the slots agree with it)
     for (size_t a = 0; a < EP; ++a) {
         pos[a] = (uint32_t)(uint16_t)v->plane_x[a] | ((uint32_t)(uint16_t)v->plane_y[a] << 16);

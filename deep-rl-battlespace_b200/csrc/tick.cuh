@@ -99,13 +99,22 @@ __device__ __forceinline__ int randint_from(uint32_t w, int lo, int hi) {
     return lo + (int)__umulhi(w, (uint32_t)(hi - lo + 1));
 }
 
+// k / 2^24 for a 24-bit k, exactly: place k in the top of the mantissa of a double in [1,2), subtract 1.
+__device__ __forceinline__ double unit24(uint32_t k) {
+    return __hiloint2double((int)(0x3ff00000u | (k >> 4)), (int)(k << 28)) - 1.0;
+}
+// w / 2^32, exactly, the same way
+__device__ __forceinline__ double unit32(uint32_t w) {
+    return __hiloint2double((int)(0x3ff00000u | (w >> 12)), (int)(w << 20)) - 1.0;
+}
+
 // unit draws of an agent-tick block: u[0]=shoot_u, u[1..3]=noise_u, u[4]=spread_u
 __device__ __forceinline__ void agent_tick_units(const uint32_t (&w)[4], double (&u)[5]) {
-    u[1] = (double)(w[0] >> 8) * (1.0 / 16777216.0);
-    u[2] = (double)(w[1] >> 8) * (1.0 / 16777216.0);
-    u[3] = (double)(w[2] >> 8) * (1.0 / 16777216.0);
-    u[0] = (double)(((w[0] & 0xffu) << 16) | ((w[1] & 0xffu) << 8) | (w[2] & 0xffu)) * (1.0 / 16777216.0);
-    u[4] = (double)w[3] * (1.0 / 4294967296.0);
+    u[1] = unit24(w[0] >> 8);
+    u[2] = unit24(w[1] >> 8);
+    u[3] = unit24(w[2] >> 8);
+    u[0] = unit24(((w[0] & 0xffu) << 16) | ((w[1] & 0xffu) << 8) | (w[2] & 0xffu));
+    u[4] = unit32(w[3]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -180,29 +189,56 @@ __device__ __forceinline__ float div360_f32(double rel) {
 
 // rel_angle / 360 -- battle_env.py:38-52,231 ; dist / diag * 2 - 1 -- battle_env.py:54-58,230.
 // atan2, the % 2pi, degrees() and the sqrt were evaluated by the host for every integer (dx, dy);
-// what is left is the part that depends on the observer's direction.  Returns (od, oa).
-__device__ __forceinline__ float2 pair_obs(const Params &p, int dx, int dy, double a0) {
-    const float od = __ldg(p.odt + abs(dy) * OD_W + abs(dx));
-    const double t = __ldg(p.t360 + (dy + T_DY) * T_W + (dx + T_DX));
+// what is left is the part that depends on the observer's direction.
+// The look-ups depend on positions only, which are final once the planes have moved, so they are
+// issued (ObsLoads) before the bullet outcome is settled and consumed after it: the L2 latency of
+// the gathers hides behind tick_end instead of stalling the warp.
+template <int N>
+struct ObsLoads {
+    double t[N + 1];
+    float od[N + 1];
+};
+
+__device__ __forceinline__ void pair_load(const Params &p, int dx, int dy, double &t, float &od) {
+    od = __ldg(p.odt + abs(dy) * OD_W + abs(dx));
+    t = __ldg(p.t360 + (dy + T_DY) * T_W + (dx + T_DX));
+}
+
+__device__ __forceinline__ float pair_angle(double t, double a0) {
     double rel = 180 + a0 - t;
     if (rel < -180) rel += 360;
     if (rel > 180) rel -= 360;
-    return make_float2(od, div360_f32(rel));
+    return div360_f32(rel);
 }
 
-// observe -- battle_env.py:202-244, for the lane's own plane; needs a fresh gather().
+// needs enemy POSITIONS from a gather() after the move (hp may still change)
 template <int N>
-__device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float (&o)[3 * N + 2]) {
+__device__ __forceinline__ void observe_issue(const Params &p, const Lane<N> &s, ObsLoads<N> &q) {
     // every lane issues all its table loads (dead planes keep an on-field position); selects follow
+    pair_load(p, s.x - s.ebx, s.y - s.eby, q.t[0], q.od[0]);
+#pragma unroll
+    for (int j = 0; j < N; ++j)
+        pair_load(p, s.x - (int)(s.exy[j] & 0xffffu), s.y - (int)(s.exy[j] >> 16), q.t[j + 1], q.od[j + 1]);
+}
+
+// observe -- battle_env.py:202-244, for the lane's own plane; needs the final s.hp / s.am
+template <int N>
+__device__ __forceinline__ void observe_finish(const Lane<N> &s, const ObsLoads<N> &q, float (&o)[3 * N + 2]) {
     const bool me = s.hp > 0;
-    float2 r = pair_obs(p, s.x - s.ebx, s.y - s.eby, s.dir);
-    o[0] = me ? r.x : -1.0f; o[1] = me ? r.y : -1.0f;
+    o[0] = me ? q.od[0] : -1.0f; o[1] = me ? pair_angle(q.t[0], s.dir) : -1.0f;
 #pragma unroll
     for (int j = 0; j < N; ++j) {
-        r = pair_obs(p, s.x - (int)(s.exy[j] & 0xffffu), s.y - (int)(s.exy[j] >> 16), s.dir);
         const bool seen = me && ((s.am >> j) & 1u);
-        o[2 + 3 * j] = seen ? 1.0f : -1.0f; o[3 + 3 * j] = seen ? r.x : -1.0f; o[4 + 3 * j] = seen ? r.y : -1.0f;
+        o[2 + 3 * j] = seen ? 1.0f : -1.0f; o[3 + 3 * j] = seen ? q.od[j + 1] : -1.0f;
+        o[4 + 3 * j] = seen ? pair_angle(q.t[j + 1], s.dir) : -1.0f;
     }
+}
+
+template <int N>
+__device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float (&o)[3 * N + 2]) {
+    ObsLoads<N> q;
+    observe_issue<N>(p, s, q);
+    observe_finish<N>(s, q, o);
 }
 
 // InstinctAgent.choose_action -- instinct/agent.py:10-62 (float32 obs decoded in double:
