@@ -180,10 +180,13 @@ __device__ __forceinline__ void gather(const Geo<N> &g, Lane<N> &s) {
 // within 2 ulp of the quotient, so float(q) can differ from float(rel / 360) only when q lies within
 // a few double ulps of a float rounding midpoint (low 29 mantissa bits == 0x10000000); only then is
 // the division itself evaluated.  The result is the reference's float in every case.
+// out of line: inlined, the compiler evaluates the division speculatively on every call
+__device__ __noinline__ float div360_exact(double rel) { return (float)(rel / 360); }
+
 __device__ __forceinline__ float div360_f32(double rel) {
     const double q = rel * (1.0 / 360.0);
     const uint32_t low = (uint32_t)__double2loint(q) & 0x1fffffffu;
-    if (low - 0x0ffffffcu <= 8u) return (float)(rel / 360);
+    if (low - 0x0ffffffcu <= 8u) return div360_exact(rel);
     return (float)q;
 }
 
