@@ -93,9 +93,14 @@ class ClockSampler:
 def cpu_port_rate(steps, warmup, envs, threads=None):
     """agent-steps/s of the CPU port (oracle/) on the same workload, all host threads."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    cores = threads or os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cores = threads or len(os.sched_getaffinity(0)) or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)   # torchrun exports OMP_NUM_THREADS=1; this arm uses every core
     from port import OracleEnv, POL_INSTINCT, POL_RANDOM
+    try:                                          # libgomp may already be loaded (torch): set it at run time too
+        import ctypes
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(cores)
+    except OSError:
+        pass
     env = OracleEnv(N_AGENTS, True, tuple(REWARDS.values()), envs, seed=0)
     for _ in range(warmup):
         env.rollout(T_TICKS, [POL_RANDOM, POL_INSTINCT])
