@@ -192,17 +192,23 @@ struct RolloutArgs {
     bs_replay rp;
     long long cursor_mod; // cursor % capacity
     long long e_mod;      // E % capacity
+    long long e0, e_end;  // env range of this launch (the host entry point pipelines chunks)
 };
 
+
+// warp-index arithmetic) and 32 resident blocks per SM give the same 32 warps as 8 blocks of 4.
+#ifndef ROLLOUT_BLOCK
+#define ROLLOUT_BLOCK 128
+#endif
 #ifndef ROLLOUT_MIN_BLOCKS
-#define ROLLOUT_MIN_BLOCKS 8
+#define ROLLOUT_MIN_BLOCKS (1024 / ROLLOUT_BLOCK)
 #endif
 template <int N, bool CONT>
-__global__ void __launch_bounds__(BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Params p, RolloutArgs ra) {
+__global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Params p, RolloutArgs ra) {
     constexpr int L = 3 * N + 2, A = CONT ? 3 : 4;
-    __shared__ WarpPool pools[WARPS];
+    __shared__ WarpPool pools[ROLLOUT_BLOCK / 32];
     WarpPool &w = pools[threadIdx.x >> 5];
-    Geo<N> g(global_warp(), p.E);
+    Geo<N> g(global_warp(), ra.e_end, ra.e0);
     Lane<N> s;
     double ret0, ret1;
     load_lane(p, g, s, nullptr, ret0, ret1);
@@ -351,6 +357,9 @@ struct bs_handle {
     ObsTables tables;
     std::vector<void *> allocs;
     cudaStream_t hstream = nullptr;  // used by the *_host entry points
+    cudaStream_t cstream = nullptr;  // copy stream of bs_rollout_fused_host
+    cudaEvent_t chunk_ev[16] = {};
+    int host_chunks = 0;             // BS_HOST_CHUNKS (tuning), 0 = default
     // device staging for *_host calls (grown on demand)
     void *stage[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t stage_sz[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -444,9 +453,9 @@ static int tie_tick_for(int n_agents) {  // battle_env.py:316-319: total_time ac
 // Kernel launch with the observation tables marked persisting in L2 for this launch only (the
 // caller's stream is not modified).
 template <class... KArgs, class... Args>
-static cudaError_t launch(const bs_handle *h, void (*kern)(KArgs...), int grid, cudaStream_t st, Args... args) {
+static cudaError_t launch(const bs_handle *h, void (*kern)(KArgs...), int grid, int block, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(BLOCK); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     if (h->tables.persist) {
         attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
@@ -460,10 +469,10 @@ static cudaError_t launch(const bs_handle *h, void (*kern)(KArgs...), int grid, 
     return cudaLaunchKernelEx(&cfg, kern, args...);
 }
 
-static inline int grid_for_envs(int64_t E, int N) {
+static inline int grid_for_envs(int64_t E, int N, int block = BLOCK) {
     const int K = 32 / (2 * N);
     const int64_t warps = (E + K - 1) / K;
-    return (int)((warps * 32 + BLOCK - 1) / BLOCK);
+    return (int)((warps * 32 + block - 1) / block);
 }
 
 #define DISPATCH_N(n_, ...)                                                  \
@@ -524,6 +533,9 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     std::vector<uint32_t> meta((size_t)n_envs, 1u << 16);
     CU(cudaMemcpy(p.meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     CU(cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&h->cstream, cudaStreamNonBlocking));
+    for (auto &ev : h->chunk_ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    if (const char *hc = getenv("BS_HOST_CHUNKS")) h->host_chunks = atoi(hc) > 15 ? 15 : atoi(hc);
     *out = h;
     return BS_OK;
 }
@@ -535,6 +547,8 @@ int bs_destroy(bs_handle *h) {
     for (void *q : h->allocs) cudaFree(q);
     for (void *q : h->stage) if (q) cudaFree(q);
     if (h->hstream) cudaStreamDestroy(h->hstream);
+    if (h->cstream) cudaStreamDestroy(h->cstream);
+    for (auto ev : h->chunk_ev) if (ev) cudaEventDestroy(ev);
     delete h;
     return BS_OK;
 }
@@ -551,8 +565,8 @@ int bs_reset(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float 
 
 static int launch_step(bs_handle *h, const StepArgs &sa, cudaStream_t st) {
     const int grid = grid_for_envs(h->E, h->N);
-    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true>, grid, st, h->p, sa))); }
-    else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false>, grid, st, h->p, sa))); }
+    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true>, grid, BLOCK, st, h->p, sa))); }
+    else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false>, grid, BLOCK, st, h->p, sa))); }
     return BS_OK;
 }
 
@@ -600,8 +614,8 @@ int bs_instinct_actions(bs_handle *h, int team, const float *obs, const double *
     return BS_OK;
 }
 
-int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue, const float *ext_actions,
-                     const bs_replay *replay, int64_t cursor, void *stream) {
+static int rollout_check(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue, const void *ext_actions,
+                         int64_t cursor) {
     if (!h) return fail(BS_E_INVALID, "null handle");
     if (T < 1) return fail(BS_E_INVALID, "T must be >= 1");
     if (learner_team != 0 && learner_team != 1) return fail(BS_E_INVALID, "learner_team must be 0 (red) or 1 (blue)");
@@ -612,9 +626,15 @@ int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int 
             return fail(BS_E_INVALID, "BS_POL_EXTERNAL needs ext_actions and is only valid for learner_team");
     }
     if (cursor < 0) return fail(BS_E_INVALID, "cursor must be >= 0");
-    DeviceGuard guard(h->device);
+    return BS_OK;
+}
+
+// launches the fused rollout for envs [e0, e_end)
+static int rollout_range(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue, const float *ext_actions,
+                         const bs_replay *replay, int64_t cursor, int64_t e0, int64_t e_end, cudaStream_t st) {
     RolloutArgs ra{};
     ra.T = T; ra.learner = learner_team; ra.pol[0] = policy_red; ra.pol[1] = policy_blue; ra.ext = ext_actions;
+    ra.e0 = e0; ra.e_end = e_end;
     if (replay && replay->capacity > 0) {
         ra.rp = *replay;
         ra.cursor_mod = cursor % replay->capacity;
@@ -622,11 +642,17 @@ int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int 
     } else {
         std::memset(&ra.rp, 0, sizeof(ra.rp));
     }
-    cudaStream_t st = (cudaStream_t)stream;
-    const int grid = grid_for_envs(h->E, h->N);
-    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, rollout_kernel<N_, true>, grid, st, h->p, ra))); }
-    else { DISPATCH_N(h->N, CU(launch(h, rollout_kernel<N_, false>, grid, st, h->p, ra))); }
+    const int grid = grid_for_envs(e_end - e0, h->N, ROLLOUT_BLOCK);
+    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, rollout_kernel<N_, true>, grid, ROLLOUT_BLOCK, st, h->p, ra))); }
+    else { DISPATCH_N(h->N, CU(launch(h, rollout_kernel<N_, false>, grid, ROLLOUT_BLOCK, st, h->p, ra))); }
     return BS_OK;
+}
+
+int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue, const float *ext_actions,
+                     const bs_replay *replay, int64_t cursor, void *stream) {
+    int rc = rollout_check(h, T, learner_team, policy_red, policy_blue, ext_actions, cursor); if (rc) return rc;
+    DeviceGuard guard(h->device);
+    return rollout_range(h, T, learner_team, policy_red, policy_blue, ext_actions, replay, cursor, 0, h->E, (cudaStream_t)stream);
 }
 
 int bs_stats(bs_handle *h, int64_t out[8], void *stream) {
@@ -854,15 +880,42 @@ int bs_instinct_actions_host(bs_handle *h, int team, const float *obs, const dou
     return BS_OK;
 }
 
+// The learner's actions arrive over PCIe (36 B per env-tick for 3v3), which takes longer than the
+// rollout itself.  The envs are therefore cut into chunks: chunk k+1's actions are copied (strided in
+// T, cudaMemcpy2DAsync on the copy stream) while chunk k's rollout runs on the compute stream.
 int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
                           const float *ext_actions, const bs_replay *replay, int64_t cursor, int64_t stats_out[8]) {
-    if (!h) return fail(BS_E_INVALID, "null handle");
-    if (T < 1) return fail(BS_E_INVALID, "T must be >= 1");
-    DeviceGuard guard(h->device);
-    const float *d_ext;
-    H2D(8, ext_actions, (size_t)T * h->E * h->N * h->A * 4, d_ext);
-    int rc = bs_rollout_fused(h, T, learner_team, policy_red, policy_blue, d_ext, replay, cursor, h->hstream);
+    int rc = rollout_check(h, T, learner_team, policy_red, policy_blue,
+                           ext_actions ? (const void *)ext_actions : (const void *)h, cursor);
     if (rc) return rc;
+    DeviceGuard guard(h->device);
+    if (!ext_actions) {
+        rc = rollout_range(h, T, learner_team, policy_red, policy_blue, nullptr, replay, cursor, 0, h->E, h->hstream);
+        if (rc) return rc;
+    } else {
+        const size_t row_bytes = (size_t)h->N * h->A * 4, pitch = (size_t)h->E * row_bytes;
+        void *d_ext = nullptr;
+        rc = stage_buf(h, 8, (size_t)T * pitch, &d_ext); if (rc) return rc;
+        const int K = 32 / h->P;
+        int chunks = h->host_chunks > 0 ? h->host_chunks : 3;   // measured best of 1..15 at 65,536 envs (profiles/r1_e2e_chunks.txt)
+        int64_t per = (h->E + chunks - 1) / chunks;
+        per = (per + K - 1) / K * K;                       // whole warps per chunk
+        if (per < 4096) per = h->E;                        // small handles: one chunk
+        int k = 0;
+        for (int64_t e0 = 0; e0 < h->E; e0 += per, ++k) {
+            const int64_t e1 = e0 + per < h->E ? e0 + per : h->E;
+            CU(cudaMemcpy2DAsync((char *)d_ext + e0 * row_bytes, pitch, (const char *)ext_actions + e0 * row_bytes, pitch,
+                                 (size_t)(e1 - e0) * row_bytes, (size_t)T, cudaMemcpyHostToDevice, h->cstream));
+            cudaEvent_t ev = h->chunk_ev[k % 16];
+            CU(cudaEventRecord(ev, h->cstream));
+            CU(cudaStreamWaitEvent(h->hstream, ev, 0));
+            rc = rollout_range(h, T, learner_team, policy_red, policy_blue, (const float *)d_ext, replay, cursor, e0, e1, h->hstream);
+            if (rc) return rc;
+        }
+        // the next call's first copy must not overtake this call's last kernel
+        CU(cudaEventRecord(h->chunk_ev[15], h->hstream));
+        CU(cudaStreamWaitEvent(h->cstream, h->chunk_ev[15], 0));
+    }
     if (stats_out) CU(cudaMemcpyAsync(stats_out, h->p.counters, 8 * sizeof(int64_t), cudaMemcpyDeviceToHost, h->hstream));
     CU(cudaStreamSynchronize(h->hstream));
     return BS_OK;

@@ -129,14 +129,15 @@ struct Geo {
     bool valid;                           // lane maps to an env < E
     long long e;                          // env index within the handle
 
-    __device__ __forceinline__ Geo(long long warp_id, long long E) {
+    // the launch covers envs [e0, e_end) of the handle
+    __device__ __forceinline__ Geo(long long warp_id, long long e_end, long long e0 = 0) {
         lane = threadIdx.x & 31;
         int sub = lane / G;
         i = lane - sub * G;
         team = i >= N;
         k = i - team * N;
-        e = warp_id * K + sub;
-        valid = sub < K && e < E;
+        e = e0 + warp_id * K + sub;
+        valid = sub < K && e < e_end;
         if (!valid) sub = 0;  // keep shuffle sources in range for idle lanes
         gb = sub * G;
         tb = gb + team * N;
@@ -527,17 +528,18 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         uint32_t P = 0, M = 0;
         if (idx < cnt_in) { P = w.pos[idx]; M = w.meta[idx]; }
         const int owner = (M >> 23) & 31;
-        int age = M >> 28;
-        bool keep = (P & B_VALID) != 0;
+        const int age = (int)(M >> 28) + 1;             // updates including this one
+        const int ai = SLOTS - age;                     // age index, 0 = oldest
+        const bool live = (P & B_VALID) != 0;
+        const bool killed = ((killmask >> owner) & 1u) && age >= 2;
+        const bool moves = live && !killed && ((runmask >> owner) & 1u);
+        bool keep = live && !killed;
         unsigned cm = 0;
-        int ai = 0;
-        if (keep && ((killmask >> owner) & 1u) && age >= 1) keep = false;
-        else if (keep && ((runmask >> owner) & 1u)) {
-            ai = SLOTS - 1 - age;
-            age += 1;
+        if (moves) {
             const uint32_t bt = w.baseT[owner];
-            if (bullet_advance(P, meta_dlt(M), age)) { atomicOr(&w.ev[owner], 1u << (2 * ai)); keep = false; }
-            else if (rect_hit((P & B_POS) - (bt & 0x07ffffffu), 67u, 64u)) { atomicOr(&w.ev[owner], 2u << (2 * ai)); keep = false; }
+            unsigned code = 0;
+            if (bullet_advance(P, meta_dlt(M), age)) code = 1u;
+            else if (rect_hit((P & B_POS) - (bt & 0x07ffffffu), 67u, 64u)) code = 2u;
             else {
                 const uint32_t Pp = (P & B_POS) - PLANE_OFF;
                 const int eb = bt >> 27;
@@ -546,8 +548,9 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
                     const uint32_t e = w.plane[eb + j];
                     cm |= ((e >> 28) != 0 && rect_hit(Pp - (e & 0x03ff07ffu), 55u, 50u) ? 1u : 0u) << j;
                 }
-                M = (M & 0x0fffffffu) | ((uint32_t)age << 28);
+                M += 1u << 28;
             }
+            if (code) { atomicOr(&w.ev[owner], code << (2 * ai)); keep = false; }
         }
         const unsigned kb = __ballot_sync(FULL, keep);
         const int nidx = out + __popc(kb & lt);

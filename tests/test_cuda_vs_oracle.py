@@ -215,3 +215,27 @@ def test_full_size_properties(cuda_device):
     for _ in range(12):
         c2.env.rollout(T, "random", "instinct")
     assert np.array_equal(c2.stats(), s)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,cont,E", [(3, True, 20000), (2, False, 17000), (3, True, 1000)])
+def test_rollout_host_pipelined_equals_device(N, cont, E, cuda_device):
+    """bs_rollout_fused_host cuts the envs into chunks and overlaps the action copy with the rollout
+    (one chunk when the handle is small); rows, state and counters must equal the one-launch path."""
+    import torch
+    from battlespace import DeviceReplay
+    from cuda_adapter import CudaEnv
+    L, A, T = 3 * N + 2, 3 if cont else 4, 8
+    a = CudaEnv(N, cont, TRAINED_REWARDS, E, seed=5)
+    b = CudaEnv(N, cont, TRAINED_REWARDS, E, seed=5)
+    ra, rb = DeviceReplay(2 * T * E, 512, N, L, A, a.dev), DeviceReplay(2 * T * E, 512, N, L, A, b.dev)
+    rng = np.random.RandomState(11)
+    for k in range(3):
+        ext = torch.from_numpy(rng.uniform(-1.2, 1.2, (T, E, N, A)).astype(np.float32))
+        a.env.rollout(T, "external", "instinct", 0, ext.to(a.dev), ra)
+        st = b.env.rollout_host(T, "external", "instinct", 0, ext.pin_memory(), rb)
+        assert np.array_equal(st, a.stats())
+    _state_equal(a.get_state(), b.get_state())
+    for x, y in ((ra.state_mem, rb.state_mem), (ra.new_state_mem, rb.new_state_mem), (ra.action_mem, rb.action_mem),
+                 (ra.rew_mem, rb.rew_mem), (ra.done_mem, rb.done_mem)):
+        assert torch.equal(x, y)
