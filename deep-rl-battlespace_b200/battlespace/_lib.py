@@ -22,7 +22,7 @@ POLICIES = {"external": POL_EXTERNAL, "random": POL_RANDOM, "instinct": POL_INST
 # every symbol include/battlespace.h declares (tests check the library exports exactly these)
 SYMBOLS = (
     "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_reset", "bs_step", "bs_step_team",
-    "bs_instinct_actions", "bs_rollout_fused", "bs_stats", "bs_stats_device", "bs_get_state",
+    "bs_step_team_replay", "bs_instinct_actions", "bs_rollout_fused", "bs_stats", "bs_stats_device", "bs_get_state",
     "bs_set_state", "bs_reset_host", "bs_step_host", "bs_step_team_host", "bs_instinct_actions_host",
     "bs_rollout_fused_host",
 )
@@ -68,6 +68,7 @@ lib.bs_destroy.argtypes = [_vp]
 lib.bs_reset.argtypes = [_vp, _vp, _vp, _vp, _vp]
 lib.bs_step.argtypes = [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_step_team.argtypes = [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
+lib.bs_step_team_replay.argtypes = [_vp, _i, _vp, _i, _i, _vp, C.POINTER(bs_replay), _i64, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_instinct_actions.argtypes = [_vp, _i, _vp, _vp, _vp, _vp]
 lib.bs_rollout_fused.argtypes = [_vp, _i, _i, _i, _i, _vp, C.POINTER(bs_replay), _i64, _vp]
 lib.bs_stats.argtypes = [_vp, _vp, _vp]

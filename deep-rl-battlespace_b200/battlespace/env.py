@@ -276,14 +276,25 @@ class parallel_env:
                           _ptr(self.done_buf), _ptr(self.env_done_buf), _ptr(self.winner_buf), self._stream()))
         return self.obs_buf, self.rew_buf, self.done_buf, self.env_done_buf, self.winner_buf
 
-    def step_team_batched(self, team_actions, learner_team=0, other_policy="instinct", draws=None):
+    def step_team_batched(self, team_actions, learner_team=0, other_policy="instinct", draws=None, replay=None,
+                          cursor=None):
         """One tick with ``learner_team``'s actions ([E,N,...]) from the caller and the other team
-        played in-kernel (main.py:179-181 with the instinct team fused into the step)."""
+        played in-kernel (main.py:179-181 with the instinct team fused into the step).  With
+        ``replay`` (a DeviceReplay) the same launch also stores the learner team's transition rows
+        (main.py:205); call ``reset_done()`` between ticks like the reference's game loop."""
         dt = self._action_dtype(team_actions, self.n_agents)
         draws = self._draws(draws)
-        check(lib.bs_step_team(self._h, int(learner_team), _ptr(team_actions), dt, POLICIES[other_policy], _ptr(draws),
-                               _ptr(self.obs_buf), _ptr(self.rew_buf), _ptr(self.done_buf), _ptr(self.env_done_buf),
-                               _ptr(self.winner_buf), self._stream()))
+        rp = None
+        if replay is not None:
+            rp = replay.as_struct()
+            if cursor is None:
+                cursor = replay.mem_cntr
+        check(lib.bs_step_team_replay(self._h, int(learner_team), _ptr(team_actions), dt, POLICIES[other_policy],
+                                      _ptr(draws), C.byref(rp) if rp is not None else None, int(cursor or 0),
+                                      _ptr(self.obs_buf), _ptr(self.rew_buf), _ptr(self.done_buf),
+                                      _ptr(self.env_done_buf), _ptr(self.winner_buf), self._stream()))
+        if replay is not None:
+            replay.mem_cntr += self._E
         return self.obs_buf, self.rew_buf, self.done_buf, self.env_done_buf, self.winner_buf
 
     def instinct_actions(self, team, obs=None, draws=None):

@@ -73,6 +73,8 @@ struct StepArgs {
     float *obs, *rew;
     uint8_t *done, *env_done;
     int8_t *winner;
+    bs_replay rp;         // optional: store_transition for act_team (capacity 0 = off)
+    long long cursor_mod; // cursor % capacity
 };
 
 // Decode the lane's policy into (adisc, a[3], spread_u).  o = the lane's current observation
@@ -124,7 +126,10 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
     load_lane(p, g, s, &rg, ret0, ret1);
 
     float o[L];
-    const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT;  // kernel-uniform
+    const bool writer = g.valid && sa.rp.capacity > 0 && g.team == sa.act_team;
+    long long row = 0;
+    if (sa.rp.capacity > 0) row = (sa.cursor_mod + g.e % sa.rp.capacity) % sa.rp.capacity;
+    const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT || sa.rp.capacity > 0;  // kernel-uniform
     if (need_obs) { gather(g, s); observe<N>(p, s, o); }
     else {
 #pragma unroll
@@ -133,15 +138,21 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
 
     int adisc = 0;
     double a[3] = {0, 0, 0}, spread_u = 0;
-    float raw[4];
+    float raw[4] = {0, 0, 0, 0};
     const int pol = sa.pol[g.team];
     if (g.valid) {
         const double *drow = sa.draws ? sa.draws + (g.e * P + g.i) * 5 : nullptr;
         if (pol == POL_EXTERNAL && sa.dtype != ACT_NONE) {
             const long long idx = g.e * sa.act_agents + (sa.act_agents == P ? g.i : g.k);
             if (!CONT) {
-                adisc = sa.dtype == ACT_I32 ? ((const int32_t *)sa.actions)[idx]
-                                            : argmax4((const float *)sa.actions + idx * 4);
+                if (sa.dtype == ACT_I32) {
+                    adisc = ((const int32_t *)sa.actions)[idx];
+                    if (adisc >= 0 && adisc < 4) raw[adisc] = 1.0f;
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) raw[c] = ((const float *)sa.actions)[idx * 4 + c];
+                    adisc = argmax4(raw);
+                }
             } else if (sa.dtype == ACT_F32) {
 #pragma unroll
                 for (int c = 0; c < 3; ++c) a[c] = clip1((double)((const float *)sa.actions)[idx * 3 + c]);
@@ -161,11 +172,39 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
         }
     }
 
+    if (writer) {  // ReplayBuffer.store_transition, maddpg/buffer.py:25-47: the part known before the tick
+        constexpr int A = CONT ? 3 : 4;
+        if (CONT && pol == POL_EXTERNAL) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) raw[c] = (float)a[c];
+        }
+        if (sa.rp.state) {
+            float *dst = sa.rp.state + (row * N + g.k) * L;
+#pragma unroll
+            for (int c = 0; c < L; ++c) dst[c] = o[c];
+        }
+        if (sa.rp.action) {
+#pragma unroll
+            for (int c = 0; c < A; ++c) sa.rp.action[(row * N + g.k) * A + c] = raw[c];
+        }
+    }
     double rew;
     Tally tl;
     tick<N, CONT>(p, g, s, rg, adisc, a, spread_u, rew, ret0, ret1, tl, sa.dtype == ACT_NONE);
-    if (sa.obs != nullptr) {
+    if (sa.obs != nullptr || sa.rp.capacity > 0) {
         observe<N>(p, s, o);
+        if (writer) {
+            const long long ra_i = row * N + g.k;
+            if (sa.rp.new_state) {
+                float *dst = sa.rp.new_state + ra_i * L;
+#pragma unroll
+                for (int c = 0; c < L; ++c) dst[c] = o[c];
+            }
+            if (sa.rp.reward) sa.rp.reward[ra_i] = (float)rew;
+            if (sa.rp.done) sa.rp.done[ra_i] = (uint8_t)(s.env_done || s.hp <= 0);
+        }
+    }
+    if (sa.obs != nullptr) {
         if (g.valid) {
             float *dst = sa.obs + (g.e * P + g.i) * L;
 #pragma unroll
@@ -584,21 +623,30 @@ int bs_step(bs_handle *h, const void *actions, int action_dtype, const double *d
         int rc = check_dtype(h, action_dtype); if (rc) return rc;
     }
     DeviceGuard guard(h->device);
-    StepArgs sa{actions, action_dtype, h->P, 0, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner};
+    StepArgs sa{actions, action_dtype, h->P, 0, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner, {}, 0};
+    return launch_step(h, sa, (cudaStream_t)stream);
+}
+
+int bs_step_team_replay(bs_handle *h, int learner_team, const void *team_actions, int action_dtype, int other_policy,
+                        const double *draws, const bs_replay *replay, int64_t cursor, float *obs, float *rew,
+                        uint8_t *done, uint8_t *env_done, int8_t *winner, void *stream) {
+    if (!h || !team_actions) return fail(BS_E_INVALID, "null handle or actions");
+    if (learner_team != 0 && learner_team != 1) return fail(BS_E_INVALID, "learner_team must be 0 (red) or 1 (blue)");
+    if (other_policy < BS_POL_RANDOM || other_policy > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "other_policy must be an in-kernel policy");
+    if (cursor < 0) return fail(BS_E_INVALID, "cursor must be >= 0");
+    int rc = check_dtype(h, action_dtype); if (rc) return rc;
+    DeviceGuard guard(h->device);
+    StepArgs sa{team_actions, action_dtype, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner, {}, 0};
+    sa.pol[1 - learner_team] = other_policy;
+    if (replay && replay->capacity > 0) { sa.rp = *replay; sa.cursor_mod = cursor % replay->capacity; }
     return launch_step(h, sa, (cudaStream_t)stream);
 }
 
 int bs_step_team(bs_handle *h, int learner_team, const void *team_actions, int action_dtype, int other_policy,
                  const double *draws, float *obs, float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner,
                  void *stream) {
-    if (!h || !team_actions) return fail(BS_E_INVALID, "null handle or actions");
-    if (learner_team != 0 && learner_team != 1) return fail(BS_E_INVALID, "learner_team must be 0 (red) or 1 (blue)");
-    if (other_policy < BS_POL_RANDOM || other_policy > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "other_policy must be an in-kernel policy");
-    int rc = check_dtype(h, action_dtype); if (rc) return rc;
-    DeviceGuard guard(h->device);
-    StepArgs sa{team_actions, action_dtype, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner};
-    sa.pol[1 - learner_team] = other_policy;
-    return launch_step(h, sa, (cudaStream_t)stream);
+    return bs_step_team_replay(h, learner_team, team_actions, action_dtype, other_policy, draws, nullptr, 0, obs, rew, done,
+                               env_done, winner, stream);
 }
 
 int bs_instinct_actions(bs_handle *h, int team, const float *obs, const double *draws, void *actions_out, void *stream) {

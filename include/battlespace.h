@@ -15,6 +15,7 @@
  *   bs_instinct_actions  instinct Team.choose_actions     instinct/team.py:11-14, instinct/agent.py:10-62
  *   bs_step_team         one game-loop iteration with the scripted team in-kernel
  *                                                         main.py:179-181, evaluate.py:69-70
+ *   bs_step_team_replay  the same + ReplayBuffer.store_transition   main.py:205, maddpg/buffer.py:25-47
  *   bs_rollout_fused     the whole inner game loop incl. ReplayBuffer.store_transition
  *                                                         main.py:178-213, maddpg/buffer.py:25-47
  *   bs_stats             env.team[c]['wins'], ties, total_games + report sums
@@ -133,6 +134,16 @@ int bs_step(bs_handle *h, const void *actions, int action_dtype, const double *d
 int bs_step_team(bs_handle *h, int learner_team, const void *team_actions, int action_dtype,
                  int other_policy, const double *draws, float *obs, float *rew, uint8_t *done,
                  uint8_t *env_done, int8_t *winner, void *stream);
+
+/* bs_step_team + ReplayBuffer.store_transition (main.py:205, maddpg/buffer.py:25-47) in the same
+ * launch: one row per env for learner_team at row (cursor + e) mod capacity -- state = the observation
+ * before the tick, action = the actions as given (continuous: clipped; BS_ACT_I32: one-hot),
+ * new_state / reward / done after it.  The caller resets done envs between calls (bs_reset with
+ * the env_done mask), as the reference's game loop does.  replay may be NULL (= bs_step_team). */
+int bs_step_team_replay(bs_handle *h, int learner_team, const void *team_actions, int action_dtype,
+                        int other_policy, const double *draws, const bs_replay *replay, int64_t cursor,
+                        float *obs, float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner,
+                        void *stream);
 
 /* instinct Team.choose_actions for `team`: obs [E,2N,L] f32 in; actions_out [E,N,3] f64
  * (continuous) or [E,N] i32 (discrete).  draws: NULL or [E,2N,5]. */
