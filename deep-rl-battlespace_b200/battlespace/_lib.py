@@ -68,7 +68,7 @@ lib.bs_destroy.argtypes = [_vp]
 lib.bs_reset.argtypes = [_vp, _vp, _vp, _vp, _vp]
 lib.bs_step.argtypes = [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_step_team.argtypes = [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
-lib.bs_step_team_replay.argtypes = [_vp, _i, _vp, _i, _i, _vp, C.POINTER(bs_replay), _i64, _vp, _vp, _vp, _vp, _vp, _vp]
+lib.bs_step_team_replay.argtypes = [_vp, _i, _vp, _i, _i, _vp, C.POINTER(bs_replay), _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_instinct_actions.argtypes = [_vp, _i, _vp, _vp, _vp, _vp]
 lib.bs_rollout_fused.argtypes = [_vp, _i, _i, _i, _i, _vp, C.POINTER(bs_replay), _i64, _vp]
 lib.bs_stats.argtypes = [_vp, _vp, _vp]

@@ -277,11 +277,13 @@ class parallel_env:
         return self.obs_buf, self.rew_buf, self.done_buf, self.env_done_buf, self.winner_buf
 
     def step_team_batched(self, team_actions, learner_team=0, other_policy="instinct", draws=None, replay=None,
-                          cursor=None):
+                          cursor=None, auto_reset=False):
         """One tick with ``learner_team``'s actions ([E,N,...]) from the caller and the other team
         played in-kernel (main.py:179-181 with the instinct team fused into the step).  With
         ``replay`` (a DeviceReplay) the same launch also stores the learner team's transition rows
-        (main.py:205); call ``reset_done()`` between ticks like the reference's game loop."""
+        (main.py:205).  Either call ``reset_done()`` between ticks like the reference's game loop, or
+        pass ``auto_reset=True``: envs that finish are reset inside the same launch and ``obs`` is then
+        the new game's first observation (rew/done/env_done/winner still describe the finished one)."""
         dt = self._action_dtype(team_actions, self.n_agents)
         draws = self._draws(draws)
         rp = None
@@ -291,7 +293,7 @@ class parallel_env:
                 cursor = replay.mem_cntr
         check(lib.bs_step_team_replay(self._h, int(learner_team), _ptr(team_actions), dt, POLICIES[other_policy],
                                       _ptr(draws), C.byref(rp) if rp is not None else None, int(cursor or 0),
-                                      _ptr(self.obs_buf), _ptr(self.rew_buf), _ptr(self.done_buf),
+                                      int(bool(auto_reset)), _ptr(self.obs_buf), _ptr(self.rew_buf), _ptr(self.done_buf),
                                       _ptr(self.env_done_buf), _ptr(self.winner_buf), self._stream()))
         if replay is not None:
             replay.mem_cntr += self._E

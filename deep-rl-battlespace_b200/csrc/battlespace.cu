@@ -75,6 +75,7 @@ struct StepArgs {
     int8_t *winner;
     bs_replay rp;         // optional: store_transition for act_team (capacity 0 = off)
     long long cursor_mod; // cursor % capacity
+    int auto_reset;       // envs that finish in this tick are reset before the call returns
 };
 
 // Decode the lane's policy into (adisc, a[3], spread_u).  o = the lane's current observation
@@ -211,16 +212,31 @@ __global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
     }
+    // auto-reset (the game loop's `env.reset()` for the next game, main.py:148): rewards, dones,
+    // env_done and winner below still describe the finished game; obs is the new game's first one.
+    const bool fresh = sa.auto_reset && g.valid && s.env_done;
+    const int out_done = s.env_done, out_hp = s.hp, out_winner = s.winner;
+    if (sa.auto_reset && __any_sync(FULL, fresh)) {
+        if (fresh) { reset_lane(p, g, s, &rg, false, nullptr); ret0 = ret1 = 0; }
+        gather(g, s);
+        float o2[L];
+        observe<N>(p, s, o2);
+        if (fresh && sa.obs != nullptr) {
+            float *dst = sa.obs + (g.e * P + g.i) * L;
+#pragma unroll
+            for (int c = 0; c < L; ++c) dst[c] = o2[c];
+        }
+    }
     if (g.valid) {
         const long long ai = g.e * P + g.i;
         if (sa.rew) sa.rew[ai] = (float)rew;
-        if (sa.done) sa.done[ai] = (uint8_t)(s.env_done || s.hp <= 0);  // self.dones, battle_env.py:275,360,478,494
+        if (sa.done) sa.done[ai] = (uint8_t)(out_done || out_hp <= 0);  // self.dones, battle_env.py:275,360,478,494
         if (g.i == 0) {
-            if (sa.env_done) sa.env_done[g.e] = (uint8_t)s.env_done;
-            if (sa.winner) sa.winner[g.e] = (int8_t)s.winner;
+            if (sa.env_done) sa.env_done[g.e] = (uint8_t)out_done;
+            if (sa.winner) sa.winner[g.e] = (int8_t)out_winner;
         }
     }
-    store_lane(p, g, s, &rg, ret0, ret1, false);
+    store_lane(p, g, s, &rg, ret0, ret1, sa.auto_reset != 0);
     flush_tally<N>(p, tl);
 }
 
@@ -623,20 +639,20 @@ int bs_step(bs_handle *h, const void *actions, int action_dtype, const double *d
         int rc = check_dtype(h, action_dtype); if (rc) return rc;
     }
     DeviceGuard guard(h->device);
-    StepArgs sa{actions, action_dtype, h->P, 0, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner, {}, 0};
+    StepArgs sa{actions, action_dtype, h->P, 0, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner, {}, 0, 0};
     return launch_step(h, sa, (cudaStream_t)stream);
 }
 
 int bs_step_team_replay(bs_handle *h, int learner_team, const void *team_actions, int action_dtype, int other_policy,
-                        const double *draws, const bs_replay *replay, int64_t cursor, float *obs, float *rew,
-                        uint8_t *done, uint8_t *env_done, int8_t *winner, void *stream) {
+                        const double *draws, const bs_replay *replay, int64_t cursor, int auto_reset, float *obs,
+                        float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner, void *stream) {
     if (!h || !team_actions) return fail(BS_E_INVALID, "null handle or actions");
     if (learner_team != 0 && learner_team != 1) return fail(BS_E_INVALID, "learner_team must be 0 (red) or 1 (blue)");
     if (other_policy < BS_POL_RANDOM || other_policy > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "other_policy must be an in-kernel policy");
     if (cursor < 0) return fail(BS_E_INVALID, "cursor must be >= 0");
     int rc = check_dtype(h, action_dtype); if (rc) return rc;
     DeviceGuard guard(h->device);
-    StepArgs sa{team_actions, action_dtype, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner, {}, 0};
+    StepArgs sa{team_actions, action_dtype, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner, {}, 0, auto_reset ? 1 : 0};
     sa.pol[1 - learner_team] = other_policy;
     if (replay && replay->capacity > 0) { sa.rp = *replay; sa.cursor_mod = cursor % replay->capacity; }
     return launch_step(h, sa, (cudaStream_t)stream);
@@ -645,7 +661,7 @@ int bs_step_team_replay(bs_handle *h, int learner_team, const void *team_actions
 int bs_step_team(bs_handle *h, int learner_team, const void *team_actions, int action_dtype, int other_policy,
                  const double *draws, float *obs, float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner,
                  void *stream) {
-    return bs_step_team_replay(h, learner_team, team_actions, action_dtype, other_policy, draws, nullptr, 0, obs, rew, done,
+    return bs_step_team_replay(h, learner_team, team_actions, action_dtype, other_policy, draws, nullptr, 0, 0, obs, rew, done,
                                env_done, winner, stream);
 }
 

@@ -138,12 +138,15 @@ int bs_step_team(bs_handle *h, int learner_team, const void *team_actions, int a
 /* bs_step_team + ReplayBuffer.store_transition (main.py:205, maddpg/buffer.py:25-47) in the same
  * launch: one row per env for learner_team at row (cursor + e) mod capacity -- state = the observation
  * before the tick, action = the actions as given (continuous: clipped; BS_ACT_I32: one-hot),
- * new_state / reward / done after it.  The caller resets done envs between calls (bs_reset with
- * the env_done mask), as the reference's game loop does.  replay may be NULL (= bs_step_team). */
+ * new_state / reward / done after it.  replay may be NULL.
+ * auto_reset != 0: an env that finishes in this tick is reset (Philox spawns) before the call
+ * returns, i.e. the game loop's next env.reset() (main.py:148) is folded in: rew/done/env_done/winner
+ * and the stored row describe the finished game, obs is the first observation of the new one.
+ * auto_reset == 0: the caller resets done envs between calls (bs_reset with the env_done mask). */
 int bs_step_team_replay(bs_handle *h, int learner_team, const void *team_actions, int action_dtype,
                         int other_policy, const double *draws, const bs_replay *replay, int64_t cursor,
-                        float *obs, float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner,
-                        void *stream);
+                        int auto_reset, float *obs, float *rew, uint8_t *done, uint8_t *env_done,
+                        int8_t *winner, void *stream);
 
 /* instinct Team.choose_actions for `team`: obs [E,2N,L] f32 in; actions_out [E,N,3] f64
  * (continuous) or [E,N] i32 (discrete).  draws: NULL or [E,2N,5]. */

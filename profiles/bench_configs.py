@@ -1,0 +1,163 @@
+#!/usr/bin/env python
+"""Secondary measurements for the BASELINE.json configs that are not the bench.py headline line.
+One JSON line per case (device time with CUDA events, >= 3 warm-up iterations, inputs > L2 or L2 noted).
+Run on the GPU box:  python profiles/bench_configs.py > gpurun_out/configs.jsonl
+
+  modeA   : 3v3 continuous, 65,536 envs, single-tick bs_step with both teams' actions from HBM (SURVEY 8d Mode A)
+  cfg2    : 2v2 discrete, 4,096 envs, shipped completed_model actors (PyTorch) vs in-kernel instinct
+  cfg4    : 5v5 continuous, instinct_ff vs instinct_ff (full bullet pool), 1,048,576 envs / world, fused T=32
+  cfg5    : 3v3 discrete, 32,768 envs per GPU: PyTorch actor forward + bs_step_team_replay + reset of done envs
+"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "deep-rl-battlespace_b200"))
+from battlespace import DeviceReplay, parallel_env  # noqa: E402
+from battlespace.sharding import summarize  # noqa: E402
+
+CF = dict(hit_base_reward=1.0, hit_plane_reward=0.9, miss_punishment=-0.02, die_punishment=-0.03, lose_punishment=-0.05)
+PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+    os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+dev = torch.device("cuda:0")
+
+
+def timed(fn, iters, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def S(N):
+    return 218 * N + 16
+
+
+def mode_a():
+    N, E, A = 3, 65536, 3
+    env = parallel_env(n_agents=N, continuous_actions=True, n_envs=E, seed=0, device=dev, **CF)
+    acts = [torch.empty((E, 2 * N, A), device=dev).uniform_(-1, 1) for _ in range(8)]
+    env.reset_batched()
+    k = [0]
+
+    def f():
+        env.step_batched(acts[k[0] % 8]); env.reset_done(); k[0] += 1
+
+    def g():
+        env.step_batched(acts[k[0] % 8]); k[0] += 1
+    ms_loop = timed(f, 200)
+    env.reset_batched()
+    half = [a[:, :N].contiguous() for a in acts]
+
+    def fa():
+        env.step_team_batched(half[k[0] % 8], 0, "instinct", auto_reset=True); k[0] += 1
+    ms_auto = timed(fa, 400)
+    env.reset_batched()
+    ms_step = timed(g, 100)      # step kernel alone (few envs finish within 100 ticks)
+    L = 3 * N + 2
+    bytes_tick = 2 * N * A * 4 + 2 * N * L * 4 + 2 * N * 4 + 2 * N + 2 + 2 * S(N)
+    gbs = bytes_tick * E / (ms_step * 1e-3) / 1e9
+    return {"case": "modeA 3v3 continuous, 65536 envs, bs_step with actions from HBM", "ms_step_kernel": ms_step,
+            "ms_step_plus_reset_done": ms_loop, "ms_step_team_instinct_auto_reset": ms_auto,
+            "agent_steps_per_s_step_team_auto_reset": E * 2 * N / (ms_auto * 1e-3), "agent_steps_per_s_kernel": E * 2 * N / (ms_step * 1e-3),
+            "agent_steps_per_s_loop": E * 2 * N / (ms_loop * 1e-3), "algorithmic_bytes_per_env_tick": bytes_tick,
+            "hbm_gbs": gbs, "hbm_frac_of_measured": gbs / PEAK}
+
+
+def cfg2():
+    w = np.load(os.path.join(ROOT, "tests", "golden", "completed_model_actors.npz"))
+    E, N = 4096, 2
+    W = [{n: torch.as_tensor(w[f"plane{k}.{n}"], device=dev) for n in
+          ("fc1.weight", "fc1.bias", "bn1.weight", "bn1.bias", "fc2.weight", "fc2.bias", "bn2.weight", "bn2.bias", "pi.weight", "pi.bias")}
+         for k in range(N)]
+
+    def actor(k, x):  # maddpg/networks.py:80-85
+        g = W[k]
+        x = torch.relu(torch.nn.functional.layer_norm(x @ g["fc1.weight"].T + g["fc1.bias"], (64,), g["bn1.weight"], g["bn1.bias"]))
+        x = torch.relu(torch.nn.functional.layer_norm(x @ g["fc2.weight"].T + g["fc2.bias"], (64,), g["bn2.weight"], g["bn2.bias"]))
+        return torch.tanh(x @ g["pi.weight"].T + g["pi.bias"])
+    env = parallel_env(n_agents=N, n_envs=E, seed=0, device=dev, **CF)
+    env.reset_batched()
+
+    def f():
+        obs = env.obs_buf
+        logits = torch.stack([actor(k, obs[:, k]) for k in range(N)], 1).contiguous()
+        env.step_team_batched(logits, 0, "instinct")
+        env.reset_done()
+    ms = timed(f, 600, warm=5)
+    s = summarize(env.stats())
+    return {"case": "cfg2 2v2 discrete, completed_model actors (PyTorch eager) vs in-kernel instinct, 4096 envs",
+            "ms_per_tick": ms, "agent_steps_per_s": E * 2 * N / (ms * 1e-3), "games": s["games"],
+            "red_winrate": s["red_winrate"], "red_avg_score": s["red_avg_score"], "blue_avg_score": s["blue_avg_score"],
+            "reference_anchor": "README.md:30 ~80 % wins; scores.json tail red 12.9 / blue 5.5 (with OU noise 0.4)"}
+
+
+def cfg4():
+    N, E, T = 5, 1 << 20, 32
+    env = parallel_env(n_agents=N, continuous_actions=True, n_envs=E, seed=0, device=dev, **CF)
+    ms = timed(lambda: env.rollout(T, "instinct_ff", "instinct_ff", 0, None, None), 10)
+    st = env.get_state()
+    live = (st["bullet_pos"][..., 0] >= 0).sum(axis=(1, 2))
+    bytes_tick = 2 * S(N) / T
+    return {"case": "cfg4 5v5 continuous, instinct_ff both teams (full bullet pool), 1,048,576 envs on ONE GPU, fused T=32, no replay",
+            "ms_per_launch": ms, "agent_steps_per_s": E * T * 2 * N / (ms * 1e-3), "max_live_bullets_per_env": int(live.max()),
+            "mean_live_bullets_per_env": float(live.mean()), "pool_slots_per_env": 24 * N,
+            "hbm_gbs_state_only": bytes_tick * E * T / (ms * 1e-3) / 1e9}
+
+
+def cfg5():
+    N, E, A = 3, 32768, 4
+    L = 3 * N + 2
+    torch.manual_seed(0)
+    actors = [torch.nn.Sequential(torch.nn.Linear(L, 64), torch.nn.LayerNorm(64), torch.nn.ReLU(), torch.nn.Linear(64, 64),
+                                  torch.nn.LayerNorm(64), torch.nn.ReLU(), torch.nn.Linear(64, A), torch.nn.Tanh()).to(dev)
+              for _ in range(N)]  # maddpg/networks.py:54-85, random init
+    env = parallel_env(n_agents=N, n_envs=E, seed=0, device=dev, **CF)
+    rp = DeviceReplay(1 << 20, 512, N, L, A, dev)
+    env.reset_batched()
+
+    @torch.no_grad()
+    def f():
+        obs = env.obs_buf
+        logits = torch.stack([actors[k](obs[:, k]) for k in range(N)], 1).contiguous()
+        env.step_team_batched(logits, 0, "instinct", replay=rp, auto_reset=True)
+
+    @torch.no_grad()
+    def env_only():
+        env.step_team_batched(logits0, 0, "instinct", replay=rp, auto_reset=True)
+    ms = timed(f, 300, warm=5)
+    logits0 = torch.zeros((E, N, A), device=dev)
+    ms_env = timed(env_only, 300, warm=5)
+    # the same tick captured once in a CUDA graph (the eager loop is launch-bound: ~30 small kernels per tick)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        f(); f()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    cur0 = rp.mem_cntr
+    with torch.cuda.graph(graph):
+        f()
+    rp.mem_cntr = cur0
+    ms_graph = timed(graph.replay, 300, warm=5)   # (replay rows land on the captured cursor: timing only)
+    return {"case": "cfg5 3v3 discrete, 32768 envs/GPU: PyTorch actors (random init) + bs_step_team_replay with auto_reset",
+            "ms_per_tick_eager": ms, "agent_steps_per_s_eager": E * 2 * N / (ms * 1e-3), "ms_env_part": ms_env,
+            "env_share_eager": ms_env / ms, "ms_per_tick_cuda_graph": ms_graph,
+            "agent_steps_per_s_cuda_graph": E * 2 * N / (ms_graph * 1e-3), "env_share_cuda_graph": ms_env / ms_graph}
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["modeA", "cfg2", "cfg4", "cfg5"]
+    fns = {"modeA": mode_a, "cfg2": cfg2, "cfg4": cfg4, "cfg5": cfg5}
+    for name in which:
+        print(json.dumps(fns[name]()), flush=True)
