@@ -8,3 +8,4 @@ from .env import BattleEnv, parallel_env, tie_tick  # noqa: F401
 from .replay import DeviceReplay  # noqa: F401
 from .sharding import allreduce_stats, shard_range  # noqa: F401
 from .instinct_team import Team as InstinctTeam  # noqa: F401
+from .actors import DeviceOUNoise, TeamActors  # noqa: F401

@@ -336,6 +336,46 @@ class parallel_env:
             replay.mem_cntr += int(T) * self._E
         return out
 
+    # ----- learner team's actors in CUDA -----------------------------------------------
+    def actor_actions(self, actors, team=0, obs=None, noise=None, normals=None, reset_mask=None, out=None):
+        """Batched ``Team.choose_actions`` (maddpg/team.py:21-28): float32 [E,N,A] actions of ``team``'s
+        planes from ``actors`` (a TeamActors) on ``obs`` [E,2N,L] (default: the env's last observation).
+        ``noise``: a DeviceOUNoise to advance and add (agent.py:30-32); ``normals`` injects its draws."""
+        obs = self.obs_buf if obs is None else obs
+        if out is None:
+            out = torch.empty((self._E, self.n_agents, self.n_actions), dtype=torch.float32, device=self.device)
+        nz = None
+        if noise is not None:
+            nz = noise.as_struct(normals, reset_mask)
+            noise.step += 1
+        check(lib.bs_actor_forward(self._h, int(team), actors.as_array(), int(actors.hidden), _ptr(obs),
+                                   C.byref(nz) if nz is not None else None, _ptr(out), self._stream()))
+        return out
+
+    def rollout_actor(self, T, actors, learner_team=0, other_policy="instinct", noise=None, replay=None, cursor=None):
+        """T iterations of the training game loop (main.py:178-213) with ``learner_team`` played by
+        ``actors``: per tick actor forward -> step + store_transition + auto-reset, all on the device,
+        one native call.  Continues from the env's last observation (call ``reset_batched()`` first)."""
+        if not hasattr(self, "_act_buf"):
+            self._act_buf = torch.empty((self._E, self.n_agents, self.n_actions), dtype=torch.float32, device=self.device)
+        rp = None
+        if replay is not None:
+            rp = replay.as_struct()
+            if cursor is None:
+                cursor = replay.mem_cntr
+        nz = None
+        if noise is not None:
+            nz = noise.as_struct(None, self.env_done_buf)
+            noise.step += int(T)
+        check(lib.bs_rollout_actor(self._h, int(T), int(learner_team), actors.as_array(), int(actors.hidden),
+                                   POLICIES[other_policy], C.byref(nz) if nz is not None else None,
+                                   C.byref(rp) if rp is not None else None, int(cursor or 0), _ptr(self.obs_buf),
+                                   _ptr(self._act_buf), _ptr(self.rew_buf), _ptr(self.done_buf), _ptr(self.env_done_buf),
+                                   _ptr(self.winner_buf), self._stream()))
+        if replay is not None:
+            replay.mem_cntr += int(T) * self._E
+        return self.obs_buf, self.rew_buf, self.done_buf, self.env_done_buf, self.winner_buf
+
     # ----- statistics (battle_env.py:102-103,169-170; main.py:218-253) ---------------------------
     def stats(self):
         """int64[8]: red wins, blue wins, ties, total_games, sum red return*2^20, sum blue return*2^20,

@@ -7,7 +7,7 @@ import ctypes as C
 
 import torch
 
-from ._lib import bs_replay
+from ._lib import bs_replay, check, lib
 
 
 class DeviceReplay:
@@ -32,15 +32,21 @@ class DeviceReplay:
     def is_ready(self):
         return self.mem_cntr >= self.batch_size
 
-    def sample(self, generator=None):
-        """Uniform sample with replacement of filled rows (buffer.py:49-67).  Returns
-        (actor_states [N,B,L], states [B,N*L], actions [N,B,A], rewards [B,N],
-         actor_new_states [N,B,L], states_ [B,N*L], dones [B,N] bool) as device tensors."""
+    def sample(self, generator=None, idx=None):
+        """Uniform sample with replacement of filled rows (buffer.py:49-67) by one gather launch
+        (``bs_replay_sample``).  Returns (actor_states [N,B,L], states [B,N*L], actions [N,B,A],
+        rewards [B,N], actor_new_states [N,B,L], states_ [B,N*L], dones [B,N] bool) as device tensors."""
         max_mem = min(self.mem_cntr, self.mem_size)
-        idx = torch.randint(0, max_mem, (self.batch_size,), device=self.device, generator=generator)
-        N, L = self.n_agents, self.obs_size
-        states, states_ = self.state_mem[idx], self.new_state_mem[idx]
-        actor_states = states.view(-1, N, L).permute(1, 0, 2).contiguous()
-        actor_new_states = states_.view(-1, N, L).permute(1, 0, 2).contiguous()
-        actions = self.action_mem[idx].permute(1, 0, 2).contiguous()
-        return actor_states, states, actions, self.rew_mem[idx], actor_new_states, states_, self.done_mem[idx].bool()
+        if idx is None:
+            idx = torch.randint(0, max_mem, (self.batch_size,), device=self.device, generator=generator)
+        idx = idx.to(device=self.device, dtype=torch.int64).contiguous()
+        B, N, L, A = idx.numel(), self.n_agents, self.obs_size, self.n_actions
+        e = lambda *s, dt=torch.float32: torch.empty(s, dtype=dt, device=self.device)
+        actor_states, states, actions, rewards = e(N, B, L), e(B, N * L), e(N, B, A), e(B, N)
+        actor_new_states, states_, dones = e(N, B, L), e(B, N * L), e(B, N, dt=torch.uint8)
+        rp = self.as_struct()
+        p = lambda t: C.c_void_p(t.data_ptr())
+        check(lib.bs_replay_sample(C.byref(rp), N, L, A, p(idx), B, p(actor_states), p(states), p(actions), p(rewards),
+                                   p(actor_new_states), p(states_), p(dones),
+                                   C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return actor_states, states, actions, rewards, actor_new_states, states_, dones.bool()

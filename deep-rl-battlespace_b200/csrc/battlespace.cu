@@ -8,6 +8,7 @@
 // There is no CPU path in this library.
 #include "../../include/battlespace.h"
 #include "tick.cuh"
+#include "actor.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -386,6 +387,43 @@ __global__ void __launch_bounds__(BLOCK) instinct_kernel(Params p, int team, con
     }
 }
 
+// ReplayBuffer.sample_buffer -- maddpg/buffer.py:49-67 (row f2).  One block row per sampled index:
+// the row's N*L state words, N*A action words and N rewards / dones are gathered with consecutive
+// threads on consecutive words; the per-agent copies (actor_states[k] = columns k*L.. of state_mem)
+// are written from the same registers, so each ring row is read once.
+struct SampleArgs {
+    bs_replay rp;
+    const long long *idx;
+    long long B;
+    int N, L, A;
+    float *actor_states, *states, *actions, *rewards, *actor_new_states, *new_states;
+    uint8_t *dones;
+};
+
+__global__ void __launch_bounds__(128) replay_sample_kernel(SampleArgs sa) {
+    const int NL = sa.N * sa.L, NA = sa.N * sa.A;
+    for (long long b = blockIdx.x; b < sa.B; b += gridDim.x) {
+        long long row = sa.idx[b];
+        row = row < 0 ? 0 : (row >= sa.rp.capacity ? sa.rp.capacity - 1 : row);
+        for (int c = threadIdx.x; c < NL; c += blockDim.x) {
+            const int k = c / sa.L, j = c - k * sa.L;
+            const float v = __ldg(sa.rp.state + row * NL + c), v2 = __ldg(sa.rp.new_state + row * NL + c);
+            if (sa.states) sa.states[b * NL + c] = v;
+            if (sa.new_states) sa.new_states[b * NL + c] = v2;
+            if (sa.actor_states) sa.actor_states[((long long)k * sa.B + b) * sa.L + j] = v;
+            if (sa.actor_new_states) sa.actor_new_states[((long long)k * sa.B + b) * sa.L + j] = v2;
+        }
+        for (int c = threadIdx.x; c < NA; c += blockDim.x) {
+            const int k = c / sa.A, j = c - k * sa.A;
+            if (sa.actions) sa.actions[((long long)k * sa.B + b) * sa.A + j] = __ldg(sa.rp.action + row * NA + c);
+        }
+        if (threadIdx.x < sa.N) {
+            if (sa.rewards) sa.rewards[b * sa.N + threadIdx.x] = __ldg(sa.rp.reward + row * sa.N + threadIdx.x);
+            if (sa.dones) sa.dones[b * sa.N + threadIdx.x] = sa.rp.done[row * sa.N + threadIdx.x];
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host side: handle + C ABI
 // ------------------------------------------------------------------------------------------------
@@ -542,6 +580,39 @@ static inline int grid_for_envs(int64_t E, int N, int block = BLOCK) {
         case 8: { constexpr int N_ = 8; __VA_ARGS__; } break;                \
         default: return fail(BS_E_INVALID, "n_agents out of range");         \
     }
+
+// ---- actors (row f1) -------------------------------------------------------------------------------
+// BS_ACTOR_ROWS (tuning, read per launch): observation rows per thread, 1 (default) or 2
+static int launch_actor(bs_handle *h, const ActorArgs &aa, cudaStream_t st) {
+    const char *e = getenv("BS_ACTOR_ROWS");
+    CU(bs_launch_actor_impl(h->N, h->cont, e && e[0] == '2' ? 2 : 1, aa, st));
+    return BS_OK;
+}
+
+static int actor_args(bs_handle *h, int team, const bs_actor *actors, int hidden, const float *obs, const bs_ou_noise *noise,
+                      float *actions_out, ActorArgs *out) {
+    if (!h || !actors || !obs || !actions_out) return fail(BS_E_INVALID, "null argument");
+    if (team != 0 && team != 1) return fail(BS_E_INVALID, "team must be 0 (red) or 1 (blue)");
+    if (hidden != AH) return fail(BS_E_UNSUPPORTED, "actor kernels are built for fc1_dims == fc2_dims == 64");
+    ActorArgs aa{};
+    for (int k = 0; k < h->N; ++k) {
+        const bs_actor &a = actors[k];
+        if (!a.fc1_w || !a.fc1_b || !a.ln1_g || !a.ln1_b || !a.fc2_w || !a.fc2_b || !a.ln2_g || !a.ln2_b || !a.pi_w || !a.pi_b)
+            return fail(BS_E_INVALID, "null actor parameter");
+        aa.net[k] = ActorNet{a.fc1_w, a.fc1_b, a.ln1_g, a.ln1_b, a.fc2_w, a.fc2_b, a.ln2_g, a.ln2_b, a.pi_w, a.pi_b};
+    }
+    aa.E = h->E; aa.env_offset = h->p.env_offset;
+    aa.obs = obs; aa.obs_env_stride = (long long)h->P * h->L; aa.obs_agent0 = team * h->N; aa.n_team = h->N;
+    aa.out = actions_out;
+    if (noise) {
+        if (!noise->state) return fail(BS_E_INVALID, "bs_ou_noise.state is null");
+        aa.ou_state = noise->state; aa.normals = noise->normals; aa.reset_mask = noise->reset_mask;
+        aa.mu = noise->mu; aa.theta = noise->theta; aa.sigma = noise->sigma; aa.scale = noise->scale;
+        aa.seed_lo = (uint32_t)noise->seed; aa.seed_hi = (uint32_t)(noise->seed >> 32); aa.step = noise->step;
+    }
+    *out = aa;
+    return BS_OK;
+}
 
 extern "C" {
 
@@ -717,6 +788,58 @@ int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int 
     int rc = rollout_check(h, T, learner_team, policy_red, policy_blue, ext_actions, cursor); if (rc) return rc;
     DeviceGuard guard(h->device);
     return rollout_range(h, T, learner_team, policy_red, policy_blue, ext_actions, replay, cursor, 0, h->E, (cudaStream_t)stream);
+}
+
+int bs_actor_forward(bs_handle *h, int team, const bs_actor *actors, int hidden, const float *obs, const bs_ou_noise *noise,
+                     float *actions_out, void *stream) {
+    ActorArgs aa;
+    int rc = actor_args(h, team, actors, hidden, obs, noise, actions_out, &aa); if (rc) return rc;
+    DeviceGuard guard(h->device);
+    return launch_actor(h, aa, (cudaStream_t)stream);
+}
+
+int bs_rollout_actor(bs_handle *h, int T, int learner_team, const bs_actor *actors, int hidden, int other_policy,
+                     const bs_ou_noise *noise, const bs_replay *replay, int64_t cursor, float *obs, float *act_scratch,
+                     float *rew, uint8_t *done, uint8_t *env_done, int8_t *winner, void *stream) {
+    if (T < 1) return fail(BS_E_INVALID, "T must be >= 1");
+    if (!env_done) return fail(BS_E_INVALID, "env_done work buffer is required");
+    if (cursor < 0) return fail(BS_E_INVALID, "cursor must be >= 0");
+    ActorArgs aa;
+    int rc = actor_args(h, learner_team, actors, hidden, obs, noise, act_scratch, &aa); if (rc) return rc;
+    if (other_policy < BS_POL_RANDOM || other_policy > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "other_policy must be an in-kernel policy");
+    DeviceGuard guard(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    StepArgs sa{act_scratch, BS_ACT_F32, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, nullptr, obs, rew, done, env_done, winner, {}, 0, 1};
+    sa.pol[1 - learner_team] = other_policy;
+    if (replay && replay->capacity > 0) sa.rp = *replay;
+    for (int t = 0; t < T; ++t) {
+        if ((rc = launch_actor(h, aa, st))) return rc;
+        if (sa.rp.capacity > 0) sa.cursor_mod = (cursor + (int64_t)t * h->E) % sa.rp.capacity;
+        if ((rc = launch_step(h, sa, st))) return rc;
+        aa.step += 1;
+        if (noise) aa.reset_mask = env_done;  // envs that just finished start the next game with fresh noise
+    }
+    return BS_OK;
+}
+
+int bs_replay_sample(const bs_replay *replay, int n_agents, int obs_len, int n_actions, const int64_t *idx, int64_t batch,
+                     float *actor_states, float *states, float *actions, float *rewards, float *actor_new_states,
+                     float *new_states, uint8_t *dones, void *stream) {
+    if (!replay || !idx) return fail(BS_E_INVALID, "null argument");
+    if (batch < 1 || replay->capacity < 1) return fail(BS_E_INVALID, "batch and capacity must be >= 1");
+    if (n_agents < 1 || n_agents > BS_MAX_AGENTS || obs_len < 1 || n_actions < 1) return fail(BS_E_INVALID, "bad row shape");
+    if (!replay->state || !replay->new_state || !replay->action || !replay->reward || !replay->done)
+        return fail(BS_E_INVALID, "replay ring has a null array");
+    cudaPointerAttributes pa;
+    CU(cudaPointerGetAttributes(&pa, idx));
+    if (pa.type != cudaMemoryTypeDevice && pa.type != cudaMemoryTypeManaged) return fail(BS_E_INVALID, "idx must be a device pointer");
+    DeviceGuard guard(pa.device);
+    SampleArgs sa{*replay, (const long long *)idx, batch, n_agents, obs_len, n_actions, actor_states, states, actions, rewards,
+                  actor_new_states, new_states, dones};
+    const int grid = (int)(batch < 148 * 16 ? batch : 148 * 16);
+    replay_sample_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(sa);
+    CU(cudaGetLastError());
+    return BS_OK;
 }
 
 int bs_stats(bs_handle *h, int64_t out[8], void *stream) {

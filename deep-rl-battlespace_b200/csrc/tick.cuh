@@ -73,7 +73,7 @@ struct Ring {
 
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al. 2011); counter layout in include/battlespace.h
-__device__ __noinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+static __device__ __noinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                             uint32_t k0, uint32_t k1) {
 #pragma unroll 1
     for (int r = 0; r < 10; ++r) {
@@ -182,7 +182,7 @@ __device__ __forceinline__ void gather(const Geo<N> &g, Lane<N> &s) {
 // a few double ulps of a float rounding midpoint (low 29 mantissa bits == 0x10000000); only then is
 // the division itself evaluated.  The result is the reference's float in every case.
 // out of line: inlined, the compiler evaluates the division speculatively on every call
-__device__ __noinline__ float div360_exact(double rel) { return (float)(rel / 360); }
+static __device__ __noinline__ float div360_exact(double rel) { return (float)(rel / 360); }
 
 __device__ __forceinline__ float div360_f32(double rel) {
     const double q = rel * (1.0 / 360.0);
@@ -280,7 +280,7 @@ __device__ __forceinline__ void instinct(const float (&o)[3 * N + 2], double sho
 }
 
 // (cos, sin)(-radians(dir)) -- calc_new_xy, sprites.py:35-42.  Out of line: two call sites per tick.
-__device__ __noinline__ double2 cos_sin_dir(double dir) {
+static __device__ __noinline__ double2 cos_sin_dir(double dir) {
     double rad = -(dir * DEG2RAD);
     double sn, cs;
     sincos(rad, &sn, &cs);

@@ -18,6 +18,12 @@
  *   bs_step_team_replay  the same + ReplayBuffer.store_transition   main.py:205, maddpg/buffer.py:25-47
  *   bs_rollout_fused     the whole inner game loop incl. ReplayBuffer.store_transition
  *                                                         main.py:178-213, maddpg/buffer.py:25-47
+ *   bs_actor_forward     NetworkedAgent.choose_action for a whole team (row f1)
+ *                                                         maddpg/networks.py:54-85, maddpg/agent.py:25-33,
+ *                                                         utils/noise.py:17-21, maddpg/team.py:21-28
+ *   bs_rollout_actor     the inner game loop with the learner team played by its actors
+ *                                                         main.py:178-213
+ *   bs_replay_sample     ReplayBuffer.sample_buffer (row f2)   maddpg/buffer.py:49-67
  *   bs_stats             env.team[c]['wins'], ties, total_games + report sums
  *                                                         envs/battle_env.py:102-103,169-170; main.py:218-253
  *   bs_get_state/bs_set_state   (no reference equivalent: checkpoint + parity injection)
@@ -91,6 +97,27 @@ typedef struct bs_replay {
     int64_t capacity;   /* rows; 0 = write nothing */
 } bs_replay;
 
+/* One NetworkedAgent.actor -- ActorNetwork, maddpg/networks.py:54-85: float32 DEVICE pointers in the
+ * nn.Linear ([out,in] row-major) / nn.LayerNorm layouts of its state_dict. */
+typedef struct bs_actor {
+    const float *fc1_w, *fc1_b; /* [H,L], [H]   fc1 */
+    const float *ln1_g, *ln1_b; /* [H], [H]     bn1 (a LayerNorm, networks.py:61) */
+    const float *fc2_w, *fc2_b; /* [H,H], [H]   fc2 */
+    const float *ln2_g, *ln2_b; /* [H], [H]     bn2 */
+    const float *pi_w, *pi_b;   /* [A,H], [A]   pi */
+} bs_actor;
+
+/* OUNoise of every (env, team slot) -- utils/noise.py:4-21, added in choose_action (agent.py:30-32). */
+typedef struct bs_ou_noise {
+    float *state;              /* [E,N,A] device, updated in place */
+    const float *normals;      /* [E,N,A] device randn draws to use, or NULL: Philox + Box-Muller keyed by
+                                  (global env, step, team slot) under `seed` */
+    const uint8_t *reset_mask; /* [E] device or NULL: != 0 -> OUNoise.reset() first (main.py:150) */
+    float mu, theta, sigma, scale; /* reference defaults 0, 0.15, 0.2, 0.1 */
+    uint64_t seed;
+    uint32_t step;             /* draw index; bs_rollout_actor uses step, step+1, ... */
+} bs_ou_noise;
+
 /* Host-side view used by bs_get_state / bs_set_state (any pointer may be NULL = skip). */
 typedef struct bs_state_view {
     int16_t *plane_x, *plane_y; /* [E,2N] rect centre */
@@ -158,6 +185,38 @@ int bs_instinct_actions(bs_handle *h, int team, const float *obs, const double *
  * env-tick is written at row (cursor + t*E + e) mod capacity.  replay may be NULL. */
 int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
                      const float *ext_actions, const bs_replay *replay, int64_t cursor, void *stream);
+
+/* NetworkedAgent.choose_action for every plane of `team` in every env (maddpg/agent.py:25-33,
+ * Team.choose_actions maddpg/team.py:21-28): actions_out[e,k,:] = tanh(pi(relu(ln(fc2(relu(ln(fc1(
+ * obs[e, team*N+k, :])))))))) with actor k's parameters, float32 like the reference's network;
+ * with `noise` != NULL the OU noise is advanced and added and the result clamped to [-1,1].
+ * actors: HOST array of N structs of device pointers.  hidden must be 64 (fc1_dims == fc2_dims,
+ * params.json).  obs [E,2N,L] f32 (the layout bs_step / bs_reset write); actions_out [E,N,A] f32 --
+ * exactly what bs_step_team takes as BS_ACT_F32 (discrete: logits -> first argmax). */
+int bs_actor_forward(bs_handle *h, int team, const bs_actor *actors, int hidden, const float *obs,
+                     const bs_ou_noise *noise, float *actions_out, void *stream);
+
+/* T iterations of the training game loop with learner_team played by its actors (main.py:178-213):
+ * per tick  bs_actor_forward(obs) -> bs_step_team_replay(auto_reset = 1, row cursor + t*E + e),
+ * 2 launches per tick and no host synchronisation.  obs [E,2N,L]: in = the current observation of
+ * every env (bs_reset / the previous call), out = the observation after the last tick.
+ * act_scratch [E,N,A] f32 and env_done [E] u8 are required work buffers (last tick's values on
+ * return); rew/done/winner may be NULL.  With noise != NULL, envs that finished in the previous tick
+ * get OUNoise.reset() (reset_mask of the FIRST tick is noise->reset_mask) and draw t uses step+t. */
+int bs_rollout_actor(bs_handle *h, int T, int learner_team, const bs_actor *actors, int hidden,
+                     int other_policy, const bs_ou_noise *noise, const bs_replay *replay, int64_t cursor,
+                     float *obs, float *act_scratch, float *rew, uint8_t *done, uint8_t *env_done,
+                     int8_t *winner, void *stream);
+
+/* ReplayBuffer.sample_buffer (maddpg/buffer.py:49-67) as one gather launch: idx [B] int64 device row
+ * indices (the caller draws them: np.random.choice(max_mem, batch_size) with replacement, :51-52).
+ * Outputs (device, float32 unless noted; any may be NULL): actor_states [N,B,L], states [B,N*L],
+ * actions [N,B,A], rewards [B,N], actor_new_states [N,B,L], states_ [B,N*L], dones [B,N] u8.
+ * Needs no env handle: the ring is the caller's; the launch goes to the device that owns `idx`. */
+int bs_replay_sample(const bs_replay *replay, int n_agents, int obs_len, int n_actions,
+                     const int64_t *idx, int64_t batch,
+                     float *actor_states, float *states, float *actions, float *rewards,
+                     float *actor_new_states, float *new_states, uint8_t *dones, void *stream);
 
 /* out[8] = {red wins, blue wins, ties, total_games, sum(red episode return)*2^20,
  * sum(blue episode return)*2^20, env ticks, agent steps}; synchronises `stream`. */

@@ -156,8 +156,38 @@ def cfg5():
             "agent_steps_per_s_cuda_graph": E * 2 * N / (ms_graph * 1e-3), "env_share_cuda_graph": ms_env / ms_graph}
 
 
+def cfg5_native():
+    """cfg5 with the learner team's actors in CUDA (bs_actor_forward) and the whole game
+    loop native (bs_rollout_actor): 2 launches per tick, no PyTorch module on the path."""
+    from battlespace import DeviceOUNoise, TeamActors
+    N, E, A, T = 3, 32768, 4, 32
+    L = 3 * N + 2
+    g = torch.Generator().manual_seed(0)
+    u = lambda *s, a=1.0: ((torch.rand(*s, generator=g) * 2 - 1) * a)
+    params = [{"fc1.weight": u(64, L, a=.125), "fc1.bias": u(64, a=.125), "bn1.weight": torch.ones(64), "bn1.bias": torch.zeros(64),
+               "fc2.weight": u(64, 64, a=.125), "fc2.bias": u(64, a=.125), "bn2.weight": torch.ones(64), "bn2.bias": torch.zeros(64),
+               "pi.weight": u(A, 64, a=.003), "pi.bias": u(A, a=.003)} for _ in range(N)]   # networks.py:58-72 init
+    actors = TeamActors(params, dev)
+    out = {"case": "cfg5 native: 3v3 discrete, 32768 envs/GPU, bs_rollout_actor (CUDA actors + step + replay rows + auto-reset), T=32 ticks per call"}
+    for rows in ("1", "2"):
+        os.environ["BS_ACTOR_ROWS"] = rows
+        env = parallel_env(n_agents=N, n_envs=E, seed=0, device=dev, **CF)
+        rp = DeviceReplay(1 << 20, 512, N, L, A, dev)
+        noise = DeviceOUNoise(E, N, A, dev, seed=1)
+        env.reset_batched()
+        ms = timed(lambda: env.rollout_actor(T, actors, 0, "instinct", noise=noise, replay=rp), 20, warm=3) / T
+        ms_actor = timed(lambda: env.actor_actions(actors, team=0, out=env._act_buf), 200, warm=5)
+        flops = 2.0 * E * N * (L * 64 + 64 * 64 + 64 * A)
+        out[f"rows{rows}"] = {"ms_per_tick": ms, "agent_steps_per_s": E * 2 * N / (ms * 1e-3), "ms_actor_kernel": ms_actor,
+                             "actor_rows_per_s": E * N / (ms_actor * 1e-3), "actor_tflops_fp32": flops / (ms_actor * 1e-3) / 1e12,
+                             "actor_frac_of_fp32_fma_peak": flops / (ms_actor * 1e-3) / (148 * 128 * 2 * 1.965e9)}
+        out["games"] = int(env.stats()[3])
+    os.environ.pop("BS_ACTOR_ROWS", None)
+    return out
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["modeA", "cfg2", "cfg4", "cfg5"]
-    fns = {"modeA": mode_a, "cfg2": cfg2, "cfg4": cfg4, "cfg5": cfg5}
+    which = sys.argv[1:] or ["modeA", "cfg2", "cfg4", "cfg5", "cfg5n"]
+    fns = {"modeA": mode_a, "cfg2": cfg2, "cfg4": cfg4, "cfg5": cfg5, "cfg5n": cfg5_native}
     for name in which:
         print(json.dumps(fns[name]()), flush=True)
