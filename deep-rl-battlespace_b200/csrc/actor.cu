@@ -5,26 +5,27 @@
 
 using namespace bs;
 
-template <int N, int A, int R>
+template <int N, int A>
 static cudaError_t launch_actor_t(const ActorArgs &aa, cudaStream_t st) {
     constexpr int L = 3 * N + 2;
-    const size_t smem = ActorSmem<L, A>::bytes(R);
+    const size_t smem = ActorSmem<L, A>::bytes();
     static bool attr_set[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (!attr_set[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(actor_kernel<L, A, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(actor_kernel<L, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         attr_set[dev & 63] = true;
     }
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const long long tiles = (aa.E + ACTOR_BLOCK * R - 1) / (ACTOR_BLOCK * R);
-    const int resident = R == 1 ? 4 : 2;                                      // blocks per SM that fit
-    long long gx = ((long long)sms * resident + aa.n_team - 1) / aa.n_team;   // one resident wave over (x, k)
-    if (gx > tiles) gx = tiles;
+    const long long tiles = (aa.E + TM - 1) / TM;
+    // 3 blocks are resident per SM; give every block the same number of tiles (no ragged second pass)
+    long long slots = ((long long)sms * 3 + aa.n_team - 1) / aa.n_team;
+    const long long passes = (tiles + slots - 1) / slots;
+    long long gx = (tiles + passes - 1) / passes;
     if (gx < 1) gx = 1;
-    actor_kernel<L, A, R><<<dim3((unsigned)gx, (unsigned)aa.n_team), ACTOR_BLOCK, smem, st>>>(aa);
+    actor_kernel<L, A><<<dim3((unsigned)gx, (unsigned)aa.n_team), ACTOR_BLOCK, smem, st>>>(aa);
     return cudaGetLastError();
 }
 
@@ -33,26 +34,25 @@ static cudaError_t launch_actor_t(const ActorArgs &aa, cudaStream_t st) {
 #ifdef BS_ACTOR_N
 #define BS_CAT2(a, b) a##b
 #define BS_CAT(a, b) BS_CAT2(a, b)
-cudaError_t BS_CAT(bs_launch_actor_n, BS_ACTOR_N)(bool cont, int rows, const ActorArgs &aa, cudaStream_t st) {
+cudaError_t BS_CAT(bs_launch_actor_n, BS_ACTOR_N)(bool cont, const ActorArgs &aa, cudaStream_t st) {
     constexpr int N = BS_ACTOR_N;
-    if (rows == 2) return cont ? launch_actor_t<N, 3, 2>(aa, st) : launch_actor_t<N, 4, 2>(aa, st);
-    return cont ? launch_actor_t<N, 3, 1>(aa, st) : launch_actor_t<N, 4, 1>(aa, st);
+    return cont ? launch_actor_t<N, 3>(aa, st) : launch_actor_t<N, 4>(aa, st);
 }
 #endif
 
 #ifdef BS_ACTOR_DISPATCH
-#define BS_DECL(n) cudaError_t bs_launch_actor_n##n(bool, int, const ActorArgs &, cudaStream_t);
+#define BS_DECL(n) cudaError_t bs_launch_actor_n##n(bool, const ActorArgs &, cudaStream_t);
 BS_DECL(1) BS_DECL(2) BS_DECL(3) BS_DECL(4) BS_DECL(5) BS_DECL(6) BS_DECL(7) BS_DECL(8)
-cudaError_t bs_launch_actor_impl(int n_agents, bool cont, int rows, const ActorArgs &aa, cudaStream_t st) {
+cudaError_t bs_launch_actor_impl(int n_agents, bool cont, const ActorArgs &aa, cudaStream_t st) {
     switch (n_agents) {
-        case 1: return bs_launch_actor_n1(cont, rows, aa, st);
-        case 2: return bs_launch_actor_n2(cont, rows, aa, st);
-        case 3: return bs_launch_actor_n3(cont, rows, aa, st);
-        case 4: return bs_launch_actor_n4(cont, rows, aa, st);
-        case 5: return bs_launch_actor_n5(cont, rows, aa, st);
-        case 6: return bs_launch_actor_n6(cont, rows, aa, st);
-        case 7: return bs_launch_actor_n7(cont, rows, aa, st);
-        case 8: return bs_launch_actor_n8(cont, rows, aa, st);
+        case 1: return bs_launch_actor_n1(cont, aa, st);
+        case 2: return bs_launch_actor_n2(cont, aa, st);
+        case 3: return bs_launch_actor_n3(cont, aa, st);
+        case 4: return bs_launch_actor_n4(cont, aa, st);
+        case 5: return bs_launch_actor_n5(cont, aa, st);
+        case 6: return bs_launch_actor_n6(cont, aa, st);
+        case 7: return bs_launch_actor_n7(cont, aa, st);
+        case 8: return bs_launch_actor_n8(cont, aa, st);
     }
     return cudaErrorInvalidValue;
 }

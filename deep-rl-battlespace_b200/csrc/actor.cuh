@@ -5,19 +5,22 @@
 // and NetworkedAgent.choose_action, maddpg/agent.py:25-33 -- a += OUNoise.noise(); clamp(-1, 1)
 // (utils/noise.py:17-21: state += theta*(mu - state) + sigma*randn; noise = state*scale).
 // Every plane of a team has its OWN actor (maddpg/team.py:17-19), so the launch is a grid of
-// (row tiles) x (team slot k): block (x, k) keeps actor k's 5.4k parameters in shared memory and every
-// thread carries R observation rows through the three layers on its own -- no inter-thread traffic,
-// LayerNorm is a per-thread reduction over registers.  fc1/fc2 width is 64 (params.json; main.py).
+// (row tiles) x (team slot k): block (x, k) keeps actor k's 5.4k parameters in shared memory
+// (transposed: [in][out]) and walks tiles of 128 observation rows through the three layers.
+// fc1/fc2 width is 64 (params.json; main.py).
 //
 // Why SIMT and not tcgen05: the check for this kernel is torch's fp32 forward (allow_tf32 is off by
 // default) at 1e-5; K = 11..64 per layer and a LayerNorm between layers leave nothing a bf16/tf32 MMA
 // could do within that tolerance without a 3-pass split.  The bound is FFMA issue: 4,992 FMA per row.
 //
-// Weights are read as broadcast LDS.128 (all lanes of a warp read the same address: one wavefront),
-// 4 weights per load, each used by R rows: FMA:LDS = 4R:1.  The second hidden layer is produced by a
-// ROLLED loop over output neurons (4 at a time) and staged per thread in shared memory (column
-// [j][thread]: conflict free), because indexing a register array dynamically is not possible and
-// unrolling 4,096 FMAs would not fit the instruction cache.
+// fc1 and fc2 are register-tiled SIMT GEMMs: each of the 128 threads owns an 8-row x 8-column block
+// of the tile's [128 x 64] output (64 independent accumulators); activations sit in shared memory as
+// [k][row] and weights as [k][col], so one k-step is 4 LDS.128 (2 broadcast activation quads, 2
+// weight quads, all conflict free) for 64 FMA -- FMA:LDS = 16:1.  The first version of this file ran
+// one row per thread with broadcast weight loads (4:1) and stalled on shared-memory latency at 27 %
+// of the FMA peak (profiles/r1h_actor_*).  LayerNorm reduces a row over the 8 threads that share it
+// with three xor-shuffles (two-pass mean / variance like torch); the 64 -> A head and the noise /
+// tanh / clamp epilogue run one row per thread from the staged activations.
 #pragma once
 #include "tick.cuh"
 
@@ -49,175 +52,202 @@ struct ActorArgs {
 
 }  // namespace bs
 
-// launches actor_kernel<3N+2, cont ? 3 : 4, rows> (defined in actor.cu)
-cudaError_t bs_launch_actor_impl(int n_agents, bool cont, int rows, const bs::ActorArgs &aa, cudaStream_t st);
+// launches actor_kernel<3N+2, cont ? 3 : 4> (defined in actor.cu)
+cudaError_t bs_launch_actor_impl(int n_agents, bool cont, const bs::ActorArgs &aa, cudaStream_t st);
 
 #ifdef BS_ACTOR_KERNELS
 namespace bs {
 
+constexpr int TM = 128;      // rows per tile == threads per block
+constexpr int WP = AH + 4;   // row stride of the transposed weights [in][out]: the transposing store at block start is then
+                             // 4-way instead of 32-way bank conflicted; quads stay 16-byte aligned
+constexpr int HP = TM + 4;   // row stride of the [k][row] hidden buffer: the 8 column groups of a warp then
+                             // store their quads to distinct banks (4 wavefronts per STS.128, the minimum)
+
 template <int L, int A>
 struct ActorSmem {
-    static constexpr int LP = (L + 3) & ~3;
-    static constexpr int W1 = 0, W2 = W1 + AH * LP, W3 = W2 + AH * AH, B1 = W3 + A * AH, G1 = B1 + AH, E1 = G1 + AH,
-                         B2 = E1 + AH, G2 = B2 + AH, E2 = G2 + AH, B3 = E2 + AH, HS = B3 + 4;
-    static constexpr size_t bytes(int R) { return (size_t)(HS + AH * ACTOR_BLOCK * R) * sizeof(float); }
+    static constexpr int OS = 0, H = OS + L * TM, W1T = H + AH * HP, W2T = W1T + L * WP, W3T = W2T + AH * WP,
+                         B1 = W3T + AH * 4, G1 = B1 + AH, E1 = G1 + AH, B2 = E1 + AH, G2 = B2 + AH, E2 = G2 + AH,
+                         B3 = E2 + AH, END = B3 + 4;
+    static constexpr size_t bytes() { return (size_t)END * sizeof(float); }
 };
 
 __device__ __forceinline__ void coop_copy(float *dst, const float *src, int n) {
     for (int i = threadIdx.x; i < n; i += ACTOR_BLOCK) dst[i] = __ldg(src + i);
 }
 
-template <int L, int A, int R>
-__global__ void __launch_bounds__(ACTOR_BLOCK) actor_kernel(ActorArgs aa) {
+__device__ __forceinline__ float4 lds4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
+
+// acc[r][c] += a[r] * w[c] for the thread's 8 x 8 block
+__device__ __forceinline__ void outer8x8(float (&acc)[8][8], const float4 &alo, const float4 &ahi, const float4 &wlo,
+                                         const float4 &whi) {
+    const float a[8] = {alo.x, alo.y, alo.z, alo.w, ahi.x, ahi.y, ahi.z, ahi.w};
+    const float w[8] = {wlo.x, wlo.y, wlo.z, wlo.w, whi.x, whi.y, whi.z, whi.w};
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[r][c] = fmaf(a[r], w[c], acc[r][c]);
+}
+
+__device__ __forceinline__ void init_bias(float (&acc)[8][8], const float *b, int tc) {
+    const float4 lo = lds4(b + tc * 4), hi = lds4(b + 32 + tc * 4);
+    const float w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[r][c] = w[c];
+}
+
+// relu(LayerNorm(row)) for the 8 rows of the thread's block, then staged as H[col][row]
+__device__ __forceinline__ void ln_relu_store(float (&acc)[8][8], const float *g, const float *b, float *H, int tc, int tr) {
+    const float4 glo = lds4(g + tc * 4), ghi = lds4(g + 32 + tc * 4), blo = lds4(b + tc * 4), bhi = lds4(b + 32 + tc * 4);
+    const float gg[8] = {glo.x, glo.y, glo.z, glo.w, ghi.x, ghi.y, ghi.z, ghi.w};
+    const float bb[8] = {blo.x, blo.y, blo.z, blo.w, bhi.x, bhi.y, bhi.z, bhi.w};
+    float mean[8], rstd[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        float s = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) s += acc[r][c];
+        mean[r] = s;
+    }
+#pragma unroll
+    for (int m = 1; m < 8; m <<= 1)   // the 8 rows' reductions travel together: 8 shuffles in flight per stage
+#pragma unroll
+        for (int r = 0; r < 8; ++r) mean[r] += __shfl_xor_sync(FULL, mean[r], m);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        mean[r] *= 1.0f / AH;
+        float v = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) { const float d = acc[r][c] - mean[r]; v = fmaf(d, d, v); }
+        rstd[r] = v;
+    }
+#pragma unroll
+    for (int m = 1; m < 8; m <<= 1)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) rstd[r] += __shfl_xor_sync(FULL, rstd[r], m);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const float rs = 1.0f / sqrtf(rstd[r] * (1.0f / AH) + LN_EPS);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[r][c] = fmaxf(fmaf((acc[r][c] - mean[r]) * rs, gg[c], bb[c]), 0.0f);
+    }
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const int col = (c < 4 ? 0 : 28) + tc * 4 + c;  // columns tc*4..+3 and 32+tc*4..+3
+        *reinterpret_cast<float4 *>(H + col * HP + tr * 4) = make_float4(acc[0][c], acc[1][c], acc[2][c], acc[3][c]);
+        *reinterpret_cast<float4 *>(H + col * HP + 64 + tr * 4) = make_float4(acc[4][c], acc[5][c], acc[6][c], acc[7][c]);
+    }
+}
+
+template <int L, int A>
+__global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
     using S = ActorSmem<L, A>;
-    constexpr int LP = S::LP;
     extern __shared__ float4 smem4[];
     float *sm = reinterpret_cast<float *>(smem4);
     const int tid = threadIdx.x, k = blockIdx.y;
+    const int tc = tid & 7, tr = tid >> 3;  // column group (8 per row group), row group (16)
     const ActorNet net = aa.net[k];
 
-    // ---- actor k's parameters -> shared memory (fc1 rows padded to LP with zeros) ---------------
-    for (int i = tid; i < AH * LP; i += ACTOR_BLOCK) {
-        const int j = i / LP, c = i - j * LP;
-        sm[S::W1 + i] = c < L ? __ldg(net.fc1_w + j * L + c) : 0.0f;
+    // ---- actor k's parameters -> shared memory, transposed to [in][out] --------------------------
+    // (coalesced global reads, all issued before the first store: one memory latency, not one per element)
+    {
+        constexpr int N1 = (L * AH + ACTOR_BLOCK - 1) / ACTOR_BLOCK, N2 = AH * AH / ACTOR_BLOCK;
+        float v1[N1], v2[N2];
+#pragma unroll
+        for (int q = 0; q < N1; ++q) { const int i = tid + q * ACTOR_BLOCK; v1[q] = i < L * AH ? __ldg(net.fc1_w + i) : 0.0f; }
+#pragma unroll
+        for (int q = 0; q < N2; ++q) v2[q] = __ldg(net.fc2_w + tid + q * ACTOR_BLOCK);
+#pragma unroll
+        for (int q = 0; q < N1; ++q) { const int i = tid + q * ACTOR_BLOCK, j = i / L, c = i - j * L; if (i < L * AH) sm[S::W1T + c * WP + j] = v1[q]; }
+#pragma unroll
+        for (int q = 0; q < N2; ++q) { const int i = tid + q * ACTOR_BLOCK, j = i / AH, c = i - j * AH; sm[S::W2T + c * WP + j] = v2[q]; }
     }
-    coop_copy(sm + S::W2, net.fc2_w, AH * AH);
-    coop_copy(sm + S::W3, net.pi_w, A * AH);
+    for (int i = tid; i < AH * 4; i += ACTOR_BLOCK) { const int c = i >> 2, a = i & 3; sm[S::W3T + i] = a < A ? __ldg(net.pi_w + a * AH + c) : 0.0f; }
     coop_copy(sm + S::B1, net.fc1_b, AH); coop_copy(sm + S::G1, net.ln1_g, AH); coop_copy(sm + S::E1, net.ln1_b, AH);
     coop_copy(sm + S::B2, net.fc2_b, AH); coop_copy(sm + S::G2, net.ln2_g, AH); coop_copy(sm + S::E2, net.ln2_b, AH);
     if (tid < 4) sm[S::B3 + tid] = tid < A ? __ldg(net.pi_b + tid) : 0.0f;
-    __syncthreads();
-    const float4 *w1 = reinterpret_cast<const float4 *>(sm + S::W1);
-    const float4 *w2 = reinterpret_cast<const float4 *>(sm + S::W2);
-    float *hs = sm + S::HS;  // [AH][ACTOR_BLOCK * R]
-    constexpr int HST = ACTOR_BLOCK * R;
+    float *Os = sm + S::OS, *H = sm + S::H;
+    const float *arow = H + tr * 4, *wcol1 = sm + S::W1T + tc * 4, *wcol2 = sm + S::W2T + tc * 4;
 
-    for (long long base = (long long)blockIdx.x * HST; base < aa.E; base += (long long)gridDim.x * HST) {
-        long long e[R];
-        float o[R][LP];
+    const long long tiles = (aa.E + TM - 1) / TM;
+    // The next tile's observation row is fetched into registers while the current tile computes.
+    float onext[L];
+    auto fetch = [&](long long tile) {
+        const long long e = tile * TM + tid;
+        const bool ok = tile < tiles && e < aa.E;
+        const float *src = aa.obs + (ok ? e : 0) * aa.obs_env_stride + (long long)(aa.obs_agent0 + k) * L;
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            e[r] = base + r * ACTOR_BLOCK + tid;
-            const bool ok = e[r] < aa.E;
-            const float *src = aa.obs + (ok ? e[r] : 0) * aa.obs_env_stride + (long long)(aa.obs_agent0 + k) * L;
+        for (int c = 0; c < L; ++c) onext[c] = ok ? __ldg(src + c) : 0.0f;
+    };
+    fetch(blockIdx.x);
+    for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const long long e = tile * TM + tid;
+        const bool ok = e < aa.E;
 #pragma unroll
-            for (int c = 0; c < LP; ++c) o[r][c] = (ok && c < L) ? __ldg(src + c) : 0.0f;
-        }
-        // ---- fc1 + LayerNorm + ReLU, fully in registers --------------------------------------
-        float h[R][AH];
+        for (int c = 0; c < L; ++c) Os[c * TM + tid] = onext[c];
+        __syncthreads();  // obs tile staged (first pass: parameters too); H of the previous tile is free
+        fetch(tile + gridDim.x);
+        float acc[8][8];
+        // ---- fc1 -----------------------------------------------------------------------------------
+        init_bias(acc, sm + S::B1, tc);
 #pragma unroll
+        for (int c = 0; c < L; ++c)
+            outer8x8(acc, lds4(Os + c * TM + tr * 4), lds4(Os + c * TM + 64 + tr * 4), lds4(wcol1 + c * WP), lds4(wcol1 + c * WP + 32));
+        ln_relu_store(acc, sm + S::G1, sm + S::E1, H, tc, tr);
+        __syncthreads();
+        // ---- fc2 -----------------------------------------------------------------------------------
+        init_bias(acc, sm + S::B2, tc);
+#pragma unroll 8
+        for (int c = 0; c < AH; ++c)
+            outer8x8(acc, lds4(arow + c * HP), lds4(arow + c * HP + 64), lds4(wcol2 + c * WP), lds4(wcol2 + c * WP + 32));
+        __syncthreads();  // every thread has read h1 before it is overwritten by h2
+        ln_relu_store(acc, sm + S::G2, sm + S::E2, H, tc, tr);
+        __syncthreads();
+        // ---- pi + tanh (+ OU noise, clamp): one row per thread -------------------------------------
+        float pi[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) pi[a] = sm[S::B3 + a];
+#pragma unroll 16
         for (int j = 0; j < AH; ++j) {
-            float acc[R];
+            const float x = H[j * HP + tid];
+            const float4 w = lds4(sm + S::W3T + j * 4);
+            pi[0] = fmaf(w.x, x, pi[0]); pi[1] = fmaf(w.y, x, pi[1]); pi[2] = fmaf(w.z, x, pi[2]);
+            if (A == 4) pi[3] = fmaf(w.w, x, pi[3]);
+        }
+        if (ok) {
+            const long long orow = (e * aa.n_team + k) * A;
+            float nz[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            if (aa.ou_state != nullptr) {
+                if (aa.normals != nullptr) {
 #pragma unroll
-            for (int r = 0; r < R; ++r) acc[r] = sm[S::B1 + j];
+                    for (int a = 0; a < A; ++a) nz[a] = aa.normals[orow + a];
+                } else {  // Philox words -> Box-Muller pairs
+                    const unsigned long long g = (unsigned long long)(aa.env_offset + e);
+                    const uint4 w = philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), aa.step,
+                                                  ((uint32_t)k << 8) | PURPOSE_OU_NOISE, aa.seed_lo, aa.seed_hi);
+                    const float u0 = ((w.x >> 8) + 1) * (1.0f / 16777216.0f), u1 = (w.y >> 8) * (1.0f / 16777216.0f);
+                    const float u2 = ((w.z >> 8) + 1) * (1.0f / 16777216.0f), u3 = (w.w >> 8) * (1.0f / 16777216.0f);
+                    const float r0 = sqrtf(-2.0f * logf(u0)), r1 = sqrtf(-2.0f * logf(u2));
+                    float s0, c0, s1, c1;
+                    sincospif(2.0f * u1, &s0, &c0); sincospif(2.0f * u3, &s1, &c1);
+                    nz[0] = r0 * c0; nz[1] = r0 * s0; nz[2] = r1 * c1; nz[3] = r1 * s1;
+                }
+                const bool rst = aa.reset_mask != nullptr && aa.reset_mask[e] != 0;
 #pragma unroll
-            for (int c4 = 0; c4 < LP / 4; ++c4) {
-                const float4 w = w1[j * (LP / 4) + c4];
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    acc[r] = fmaf(w.x, o[r][4 * c4 + 0], acc[r]); acc[r] = fmaf(w.y, o[r][4 * c4 + 1], acc[r]);
-                    acc[r] = fmaf(w.z, o[r][4 * c4 + 2], acc[r]); acc[r] = fmaf(w.w, o[r][4 * c4 + 3], acc[r]);
+                for (int a = 0; a < A; ++a) {  // utils/noise.py:17-21
+                    const float x = rst ? aa.mu : aa.ou_state[orow + a];
+                    const float st = x + (aa.theta * (aa.mu - x) + aa.sigma * nz[a]);
+                    aa.ou_state[orow + a] = st;
+                    nz[a] = st * aa.scale;
                 }
             }
 #pragma unroll
-            for (int r = 0; r < R; ++r) h[r][j] = acc[r];
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            float s = 0.0f;
-#pragma unroll
-            for (int j = 0; j < AH; ++j) s += h[r][j];
-            const float mean = s * (1.0f / AH);
-            float v = 0.0f;
-#pragma unroll
-            for (int j = 0; j < AH; ++j) { const float d = h[r][j] - mean; v = fmaf(d, d, v); }
-            const float rstd = 1.0f / sqrtf(v * (1.0f / AH) + LN_EPS);
-#pragma unroll
-            for (int j = 0; j < AH; ++j)
-                h[r][j] = fmaxf(fmaf((h[r][j] - mean) * rstd, sm[S::G1 + j], sm[S::E1 + j]), 0.0f);
-        }
-        // ---- fc2: rolled over output neurons, 4 at a time; pre-norm values staged in smem ------
-        float s2[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) s2[r] = 0.0f;
-#pragma unroll 1
-        for (int j = 0; j < AH; j += 4) {
-            float acc[4][R];
-#pragma unroll
-            for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[jj][r] = sm[S::B2 + j + jj];
-#pragma unroll
-            for (int i4 = 0; i4 < AH / 4; ++i4) {
-#pragma unroll
-                for (int jj = 0; jj < 4; ++jj) {
-                    const float4 w = w2[(j + jj) * (AH / 4) + i4];
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        acc[jj][r] = fmaf(w.x, h[r][4 * i4 + 0], acc[jj][r]); acc[jj][r] = fmaf(w.y, h[r][4 * i4 + 1], acc[jj][r]);
-                        acc[jj][r] = fmaf(w.z, h[r][4 * i4 + 2], acc[jj][r]); acc[jj][r] = fmaf(w.w, h[r][4 * i4 + 3], acc[jj][r]);
-                    }
-                }
-            }
-#pragma unroll
-            for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    hs[(j + jj) * HST + r * ACTOR_BLOCK + tid] = acc[jj][r];
-                    s2[r] += acc[jj][r];
-                }
-        }
-        // ---- LayerNorm + ReLU + pi + tanh (+ OU noise, clamp) ---------------------------------
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const float mean = s2[r] * (1.0f / AH);
-            const float *col = hs + r * ACTOR_BLOCK + tid;
-            float v = 0.0f;
-#pragma unroll 8
-            for (int j = 0; j < AH; ++j) { const float d = col[j * HST] - mean; v = fmaf(d, d, v); }
-            const float rstd = 1.0f / sqrtf(v * (1.0f / AH) + LN_EPS);
-            float pi[A];
-#pragma unroll
-            for (int a = 0; a < A; ++a) pi[a] = sm[S::B3 + a];
-#pragma unroll 8
-            for (int j = 0; j < AH; ++j) {
-                const float x = fmaxf(fmaf((col[j * HST] - mean) * rstd, sm[S::G2 + j], sm[S::E2 + j]), 0.0f);
-#pragma unroll
-                for (int a = 0; a < A; ++a) pi[a] = fmaf(sm[S::W3 + a * AH + j], x, pi[a]);
-            }
-            if (e[r] < aa.E) {
-                const long long orow = (e[r] * aa.n_team + k) * A;
-                float nz[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-                if (aa.ou_state != nullptr) {
-                    if (aa.normals != nullptr) {
-#pragma unroll
-                        for (int a = 0; a < A; ++a) nz[a] = aa.normals[orow + a];
-                    } else {  // Philox words -> Box-Muller pairs
-                        const unsigned long long g = (unsigned long long)(aa.env_offset + e[r]);
-                        const uint4 w = philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), aa.step,
-                                                      ((uint32_t)k << 8) | PURPOSE_OU_NOISE, aa.seed_lo, aa.seed_hi);
-                        const float u0 = ((w.x >> 8) + 1) * (1.0f / 16777216.0f), u1 = (w.y >> 8) * (1.0f / 16777216.0f);
-                        const float u2 = ((w.z >> 8) + 1) * (1.0f / 16777216.0f), u3 = (w.w >> 8) * (1.0f / 16777216.0f);
-                        const float r0 = sqrtf(-2.0f * logf(u0)), r1 = sqrtf(-2.0f * logf(u2));
-                        float s0, c0, s1, c1;
-                        sincospif(2.0f * u1, &s0, &c0); sincospif(2.0f * u3, &s1, &c1);
-                        nz[0] = r0 * c0; nz[1] = r0 * s0; nz[2] = r1 * c1; nz[3] = r1 * s1;
-                    }
-                    const bool rst = aa.reset_mask != nullptr && aa.reset_mask[e[r]] != 0;
-#pragma unroll
-                    for (int a = 0; a < A; ++a) {  // utils/noise.py:17-21
-                        const float x = rst ? aa.mu : aa.ou_state[orow + a];
-                        const float st = x + (aa.theta * (aa.mu - x) + aa.sigma * nz[a]);
-                        aa.ou_state[orow + a] = st;
-                        nz[a] = st * aa.scale;
-                    }
-                }
-#pragma unroll
-                for (int a = 0; a < A; ++a) {
-                    float act = tanhf(pi[a]);
-                    if (aa.ou_state != nullptr) act = fminf(fmaxf(act + nz[a], -1.0f), 1.0f);  // agent.py:31-32
-                    aa.out[orow + a] = act;
-                }
+            for (int a = 0; a < A; ++a) {
+                float act = tanhf(pi[a]);
+                if (aa.ou_state != nullptr) act = fminf(fmaxf(act + nz[a], -1.0f), 1.0f);  // agent.py:31-32
+                aa.out[orow + a] = act;
             }
         }
     }

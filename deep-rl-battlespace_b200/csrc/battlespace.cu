@@ -582,10 +582,8 @@ static inline int grid_for_envs(int64_t E, int N, int block = BLOCK) {
     }
 
 // ---- actors (row f1) -------------------------------------------------------------------------------
-// BS_ACTOR_ROWS (tuning, read per launch): observation rows per thread, 1 (default) or 2
 static int launch_actor(bs_handle *h, const ActorArgs &aa, cudaStream_t st) {
-    const char *e = getenv("BS_ACTOR_ROWS");
-    CU(bs_launch_actor_impl(h->N, h->cont, e && e[0] == '2' ? 2 : 1, aa, st));
+    CU(bs_launch_actor_impl(h->N, h->cont, aa, st));
     return BS_OK;
 }
 

@@ -169,8 +169,7 @@ def cfg5_native():
                "pi.weight": u(A, 64, a=.003), "pi.bias": u(A, a=.003)} for _ in range(N)]   # networks.py:58-72 init
     actors = TeamActors(params, dev)
     out = {"case": "cfg5 native: 3v3 discrete, 32768 envs/GPU, bs_rollout_actor (CUDA actors + step + replay rows + auto-reset), T=32 ticks per call"}
-    for rows in ("1", "2"):
-        os.environ["BS_ACTOR_ROWS"] = rows
+    for rows in ("1",):
         env = parallel_env(n_agents=N, n_envs=E, seed=0, device=dev, **CF)
         rp = DeviceReplay(1 << 20, 512, N, L, A, dev)
         noise = DeviceOUNoise(E, N, A, dev, seed=1)
@@ -178,11 +177,10 @@ def cfg5_native():
         ms = timed(lambda: env.rollout_actor(T, actors, 0, "instinct", noise=noise, replay=rp), 20, warm=3) / T
         ms_actor = timed(lambda: env.actor_actions(actors, team=0, out=env._act_buf), 200, warm=5)
         flops = 2.0 * E * N * (L * 64 + 64 * 64 + 64 * A)
-        out[f"rows{rows}"] = {"ms_per_tick": ms, "agent_steps_per_s": E * 2 * N / (ms * 1e-3), "ms_actor_kernel": ms_actor,
+        out["native"] = {"ms_per_tick": ms, "agent_steps_per_s": E * 2 * N / (ms * 1e-3), "ms_actor_kernel": ms_actor,
                              "actor_rows_per_s": E * N / (ms_actor * 1e-3), "actor_tflops_fp32": flops / (ms_actor * 1e-3) / 1e12,
                              "actor_frac_of_fp32_fma_peak": flops / (ms_actor * 1e-3) / (148 * 128 * 2 * 1.965e9)}
         out["games"] = int(env.stats()[3])
-    os.environ.pop("BS_ACTOR_ROWS", None)
     return out
 
 
