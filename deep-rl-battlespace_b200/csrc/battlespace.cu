@@ -118,8 +118,11 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
     }
 }
 
+#ifndef STEP_MIN_BLOCKS
+#define STEP_MIN_BLOCKS 6
+#endif
 template <int N, bool CONT>
-__global__ void __launch_bounds__(BLOCK) step_kernel(Params p, StepArgs sa) {
+__global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, StepArgs sa) {
     constexpr int P = 2 * N, L = 3 * N + 2;
     __shared__ Ring rg;
     Geo<N> g(global_warp(), p.E);

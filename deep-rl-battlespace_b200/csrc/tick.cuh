@@ -287,13 +287,51 @@ static __device__ __noinline__ double2 cos_sin_dir(double dir) {
     return make_double2(cs, sn);
 }
 
+// fp32 speculation for the two places where a cosine only feeds a truncation (plane move, bullet
+// step).  (cos, sin)(-radians(dir)) with the argument reduced in double and MUFU sin/cos in float:
+// absolute error <= 2^-21.2 (MUFU on [-pi, pi]) + 1.9e-7 (float(rad)) < 7e-7, i.e. < 3.2e-5 px after the
+// multiplication by <= 45.  floor_guarded() accepts the float result only when it is at least FLOOR_GUARD
+// (8x that bound) away from an integer -- then floor() of the exact double product is the same integer
+// -- and otherwise the caller takes the exact double path (about 1 lane-call in 2,000).
+constexpr float FLOOR_GUARD = 2.5e-4f;
+
+__device__ __forceinline__ void cos_sin_fast(double dir, float &cs, float &sn) {
+    double rad = -(dir * DEG2RAD);       // dir in [-4, 364]: rad in [-6.36, 0.07]
+    if (rad < -PI) rad += TWO_PI;        // -> [-pi, pi]
+    const float r = (float)rad;
+    cs = __cosf(r); sn = __sinf(r);
+}
+
+__device__ __forceinline__ bool floor_guarded(float v, int &fl) {
+    const float f = floorf(v), fr = v - f;
+    fl = (int)f;
+    return fr > FLOOR_GUARD && fr < 1.0f - FLOOR_GUARD;
+}
+
 // Plane.forward + clamp -- sprites.py:123-141 (rect.center = floats: C cast, then the
-// screen clamp; centre x in [25,1175], y in [24,776] for the 50x48 sprite)
+// screen clamp; centre x in [25,1175], y in [24,776] for the 50x48 sprite).
+// FAST (continuous mode; in discrete mode the directions are multiples of 15 degrees and hit exact
+// integers all the time): x + st*cos >= 25 - 27.5, and any negative sum clamps to 25 whether it is
+// truncated or floored, so trunc(x + v) == x + floor(v) for the purpose of the clamped result.
+template <bool FAST>
 __device__ __forceinline__ void plane_forward(int &x, int &y, double dir, double speed) {
-    double2 cssn = cos_sin_dir(dir);
-    double st = speed * 0.1;
-    int nx = (int)((double)x + st * cssn.x);
-    int ny = (int)((double)y + st * cssn.y);
+    const double st = speed * 0.1;
+    int nx, ny;
+    bool done = false;
+    if (FAST) {
+        float cs, sn;
+        cos_sin_fast(dir, cs, sn);
+        const float stf = (float)st;
+        int fx, fy;
+        const bool okx = floor_guarded(stf * cs, fx), oky = floor_guarded(stf * sn, fy);
+        done = okx && oky;
+        nx = x + fx; ny = y + fy;
+    }
+    if (!done) {
+        double2 cssn = cos_sin_dir(dir);
+        nx = (int)((double)x + st * cssn.x);
+        ny = (int)((double)y + st * cssn.y);
+    }
     x = min(max(nx, 25), 1175);
     y = min(max(ny, 24), 776);
 }
@@ -377,7 +415,7 @@ __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lan
             if (adisc == 2) mdir = plane_rotate(s.dir, 15);
             if (adisc == 3) mdir = plane_rotate(s.dir, -15);
         }
-        if (move) plane_forward(s.x, s.y, mdir, speed);
+        if (move) plane_forward<CONT>(s.x, s.y, mdir, speed);
         if (CONT) { s.dir = plane_rotate(s.dir, a[1] * 35); shoot = a[2] > 0; }
         else s.dir = mdir;
     }
@@ -386,12 +424,24 @@ __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lan
     // a result in (-1,0) truncates to 0 (flagged "exact" when d itself is an integer).
     c.spawnP = 0; c.spawnD = 0;
     if (shoot) {
-        double2 cssn = cos_sin_dir(d0 + (spread_u * 8 - 4));
-        double ddx = (450 * 0.1) * cssn.x, ddy = (450 * 0.1) * cssn.y;
-        double fx = floor(ddx), fy = floor(ddy);
-        c.spawnP = (((uint32_t)x0 | ((uint32_t)y0 << 16)) + B_BIAS) | B_VALID | (fx == ddx ? B_XEXACT : 0u) |
-                   (fy == ddy ? B_YEXACT : 0u);
-        c.spawnD = (int)fx + (int)fy * 65536;
+        const double bdir = d0 + (spread_u * 8 - 4);
+        const uint32_t at = (((uint32_t)x0 | ((uint32_t)y0 << 16)) + B_BIAS) | B_VALID;
+        bool done = false;
+        if (CONT) {  // fp32 speculation, see cos_sin_fast: a guarded floor is never an exact integer
+            float cs, sn;
+            cos_sin_fast(bdir, cs, sn);
+            int fx, fy;
+            const bool okx = floor_guarded(45.0f * cs, fx), oky = floor_guarded(45.0f * sn, fy);
+            done = okx && oky;
+            c.spawnP = at; c.spawnD = fx + fy * 65536;
+        }
+        if (!done) {
+            double2 cssn = cos_sin_dir(bdir);
+            double ddx = (450 * 0.1) * cssn.x, ddy = (450 * 0.1) * cssn.y;
+            double fx = floor(ddx), fy = floor(ddy);
+            c.spawnP = at | (fx == ddx ? B_XEXACT : 0u) | (fy == ddy ? B_YEXACT : 0u);
+            c.spawnD = (int)fx + (int)fy * 65536;
+        }
     }
 }
 
