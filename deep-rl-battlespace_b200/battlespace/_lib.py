@@ -24,7 +24,7 @@ SYMBOLS = (
     "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_reset", "bs_step", "bs_step_team",
     "bs_step_team_replay", "bs_instinct_actions", "bs_rollout_fused", "bs_stats", "bs_stats_device", "bs_get_state",
     "bs_set_state", "bs_reset_host", "bs_step_host", "bs_step_team_host", "bs_instinct_actions_host",
-    "bs_rollout_fused_host", "bs_actor_forward", "bs_rollout_actor", "bs_replay_sample",
+    "bs_rollout_fused_host", "bs_actor_forward", "bs_rollout_actor", "bs_replay_sample", "bs_render",
 )
 
 
@@ -57,6 +57,10 @@ class bs_ou_noise(C.Structure):
     _fields_ = [("state", C.c_void_p), ("normals", C.c_void_p), ("reset_mask", C.c_void_p),
                 ("mu", C.c_float), ("theta", C.c_float), ("sigma", C.c_float), ("scale", C.c_float),
                 ("seed", C.c_uint64), ("step", C.c_uint32)]
+
+
+class bs_sprites(C.Structure):
+    _fields_ = [("plane", C.c_void_p * 2), ("base", C.c_void_p * 2)]
 
 
 STATE_FIELDS = ("plane_x", "plane_y", "plane_dir", "plane_hp", "base_pos", "base_hp", "bullet_pos",
@@ -97,6 +101,7 @@ lib.bs_actor_forward.argtypes = [_vp, _i, C.POINTER(bs_actor), _i, _vp, C.POINTE
 lib.bs_rollout_actor.argtypes = [_vp, _i, _i, C.POINTER(bs_actor), _i, _i, C.POINTER(bs_ou_noise), C.POINTER(bs_replay), _i64,
                                  _vp, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_replay_sample.argtypes = [C.POINTER(bs_replay), _i, _i, _i, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
+lib.bs_render.argtypes = [_vp, _i64, C.POINTER(bs_sprites), _vp, _vp]
 for _name in SYMBOLS:
     if _name not in ("bs_version", "bs_last_error"):
         getattr(lib, _name).restype = _i

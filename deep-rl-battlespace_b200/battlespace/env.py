@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import numpy as np
 import torch
@@ -197,6 +198,8 @@ class parallel_env:
             self.agents = [a for i, a in enumerate(self.possible_agents) if not done[0, i]]
         rewards = {a: (float(rew[0, i]) if rew[0, i] != 0 else 0) for i, a in enumerate(self.possible_agents)}
         infos = {a: {} for a in self.possible_agents}
+        if self.show:  # battle_env.py:375-376
+            self.render()
         return self._obs_dict(obs), rewards, self.dones, infos
 
     def wins(self):
@@ -209,18 +212,41 @@ class parallel_env:
 
     # rendering stays on the host and off the hot path (battle_env.py:426-447,498-580); this box has
     # no graphics stack, so these keep the call surface and do nothing.
+    # ----- rendering (battle_env.py:498-581): headless CUDA frames, no window ---------
+    def render_frame(self, env=0, out=None, sprites=None):
+        """RGB uint8 [800,1200,3] device tensor of env ``env`` as ``render()`` would draw it."""
+        from .render import Sprites
+        if sprites is not None:
+            self._sprites = sprites
+        if getattr(self, "_sprites", None) is None:
+            self._sprites = Sprites(self.device, os.environ.get("BATTLESPACE_ASSETS"))
+        if out is None:
+            out = torch.empty((self.height, self.width, 3), dtype=torch.uint8, device=self.device)
+        check(lib.bs_render(self._h, int(env), C.byref(self._sprites.struct), _ptr(out), self._stream()))
+        return out
+
     def render(self, mode="human"):
-        return None
+        """The reference opens a pygame window (unavailable here); this keeps its contract for the
+        callers that matter: nothing unless ``show``; when recording, one frame of env 0 per call."""
+        if not self.show:
+            return None
+        frame = self.render_frame(0)
+        if self.recording and getattr(self, "video", None) is not None:
+            self.video.update(frame.cpu().numpy())
+        return frame
 
     def winner_screen(self):
         return None
 
     def start_recording(self, path):
+        from .render import VideoSink
         self.recording = True
+        self.video = VideoSink(path, self.fps)
 
     def export_video(self):
         if self.recording:
             self.recording = False
+            self.video.export()
         else:
             print("Not recording!")
 

@@ -9,6 +9,7 @@
 #include "../../include/battlespace.h"
 #include "tick.cuh"
 #include "actor.cuh"
+#include "render.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -839,6 +840,18 @@ int bs_replay_sample(const bs_replay *replay, int n_agents, int obs_len, int n_a
                   actor_new_states, new_states, dones};
     const int grid = (int)(batch < 148 * 16 ? batch : 148 * 16);
     replay_sample_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(sa);
+    CU(cudaGetLastError());
+    return BS_OK;
+}
+
+int bs_render(bs_handle *h, int64_t env, const bs_sprites *sprites, uint8_t *rgb, void *stream) {
+    if (!h || !sprites || !rgb) return fail(BS_E_INVALID, "null argument");
+    if (env < 0 || env >= h->E) return fail(BS_E_INVALID, "env index out of range");
+    if (!sprites->plane[0] || !sprites->plane[1] || !sprites->base[0] || !sprites->base[1]) return fail(BS_E_INVALID, "null sprite");
+    DeviceGuard guard(h->device);
+    RenderArgs ra{env, {sprites->plane[0], sprites->plane[1]}, {sprites->base[0], sprites->base[1]}, rgb};
+    const int grid = (R_W * R_H + 255) / 256;
+    DISPATCH_N(h->N, render_kernel<N_><<<grid, 256, 0, (cudaStream_t)stream>>>(h->p, ra));
     CU(cudaGetLastError());
     return BS_OK;
 }

@@ -24,6 +24,8 @@
  *   bs_rollout_actor     the inner game loop with the learner team played by its actors
  *                                                         main.py:178-213
  *   bs_replay_sample     ReplayBuffer.sample_buffer (row f2)   maddpg/buffer.py:49-67
+ *   bs_render            parallel_env.render into a device RGB buffer (row f4; no window)
+ *                                                         envs/battle_env.py:498-560, envs/sprites.py:155-178,265-278,353-360
  *   bs_stats             env.team[c]['wins'], ties, total_games + report sums
  *                                                         envs/battle_env.py:102-103,169-170; main.py:218-253
  *   bs_get_state/bs_set_state   (no reference equivalent: checkpoint + parity injection)
@@ -217,6 +219,20 @@ int bs_replay_sample(const bs_replay *replay, int n_agents, int obs_len, int n_a
                      const int64_t *idx, int64_t batch,
                      float *actor_states, float *states, float *actions, float *rewards,
                      float *actor_new_states, float *new_states, uint8_t *dones, void *stream);
+
+/* Sprites for bs_render: RGBA8 DEVICE images in the sizes of the reference's assets (sprites.py:61,226:
+ * plane 50 wide x 48 high, base 62 x 62), index 0 = red, 1 = blue. */
+typedef struct bs_sprites {
+    const uint8_t *plane[2]; /* [48][50][4] */
+    const uint8_t *base[2];  /* [62][62][4] */
+} bs_sprites;
+
+/* parallel_env.render (battle_env.py:498-560) for env `env` into rgb [800][1200][3] u8 (device), no
+ * window: white background, bullets as 6x3 quads in the shooter's colour, both bases and the alive
+ * planes (sprites rotated counter-clockwise by their direction about the rect centre, nearest
+ * neighbour) with their hp bars.  Left out: explosion animation, plane names / winner text (fonts),
+ * rounded bar corners.  Integer geometry (half-pixels, Q14 rotation): reproducible bit for bit. */
+int bs_render(bs_handle *h, int64_t env, const bs_sprites *sprites, uint8_t *rgb, void *stream);
 
 /* out[8] = {red wins, blue wins, ties, total_games, sum(red episode return)*2^20,
  * sum(blue episode return)*2^20, env ticks, agent steps}; synchronises `stream`. */
