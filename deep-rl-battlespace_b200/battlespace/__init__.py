@@ -9,3 +9,4 @@ from .replay import DeviceReplay  # noqa: F401
 from .sharding import allreduce_stats, shard_range  # noqa: F401
 from .instinct_team import Team as InstinctTeam  # noqa: F401
 from .actors import DeviceOUNoise, TeamActors  # noqa: F401
+from .stats import EpisodeLog  # noqa: F401

@@ -24,7 +24,7 @@ SYMBOLS = (
     "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_reset", "bs_step", "bs_step_team",
     "bs_step_team_replay", "bs_instinct_actions", "bs_rollout_fused", "bs_stats", "bs_stats_device", "bs_get_state",
     "bs_set_state", "bs_reset_host", "bs_step_host", "bs_step_team_host", "bs_instinct_actions_host",
-    "bs_rollout_fused_host", "bs_actor_forward", "bs_rollout_actor", "bs_replay_sample", "bs_render",
+    "bs_rollout_fused_host", "bs_actor_forward", "bs_rollout_actor", "bs_replay_sample", "bs_render", "bs_episode_log", "bs_episode_log_count",
 )
 
 
@@ -102,6 +102,8 @@ lib.bs_rollout_actor.argtypes = [_vp, _i, _i, C.POINTER(bs_actor), _i, _i, C.POI
                                  _vp, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_replay_sample.argtypes = [C.POINTER(bs_replay), _i, _i, _i, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_render.argtypes = [_vp, _i64, C.POINTER(bs_sprites), _vp, _vp]
+lib.bs_episode_log.argtypes = [_vp, _vp, _i64]
+lib.bs_episode_log_count.argtypes = [_vp, C.POINTER(_i64), _vp]
 for _name in SYMBOLS:
     if _name not in ("bs_version", "bs_last_error"):
         getattr(lib, _name).restype = _i

@@ -650,13 +650,14 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
         (rc = dalloc(h, &p.base_pos, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.base_hp, (size_t)n_envs * 2)) ||
         (rc = dalloc(h, &p.bul_pos, EP * SLOTS)) || (rc = dalloc(h, &p.bul_dlt, EP * SLOTS)) ||
         (rc = dalloc(h, &p.meta, (size_t)n_envs)) || (rc = dalloc(h, &p.episode, (size_t)n_envs)) ||
-        (rc = dalloc(h, &p.ret, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.counters, 8))) {
+        (rc = dalloc(h, &p.ret, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.counters, 9))) {
         bs_destroy(h);
         return rc;
     }
     ObsTables tb;
     if ((rc = obs_tables_for(device, &tb))) { bs_destroy(h); return rc; }
     p.t360 = tb.t360; p.odt = tb.odt; h->tables = tb;
+    p.ep_log = nullptr; p.ep_cap = 0;
     // every env starts "done" (nothing spawned yet): the first reset / rollout tick spawns it
     std::vector<uint32_t> meta((size_t)n_envs, 1u << 16);
     CU(cudaMemcpy(p.meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
@@ -853,6 +854,22 @@ int bs_render(bs_handle *h, int64_t env, const bs_sprites *sprites, uint8_t *rgb
     const int grid = (R_W * R_H + 255) / 256;
     DISPATCH_N(h->N, render_kernel<N_><<<grid, 256, 0, (cudaStream_t)stream>>>(h->p, ra));
     CU(cudaGetLastError());
+    return BS_OK;
+}
+
+int bs_episode_log(bs_handle *h, float *log, int64_t capacity) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    if (log && (capacity < 1 || (capacity & (capacity - 1)) != 0)) return fail(BS_E_INVALID, "capacity must be a power of two");
+    h->p.ep_log = log; h->p.ep_cap = log ? capacity : 0;
+    return BS_OK;
+}
+
+int bs_episode_log_count(bs_handle *h, int64_t *count, void *stream) {
+    if (!h || !count) return fail(BS_E_INVALID, "null argument");
+    DeviceGuard guard(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaMemcpyAsync(count, h->p.counters + 8, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
     return BS_OK;
 }
 

@@ -54,11 +54,15 @@ struct Params {
     uint32_t *meta;       // [E]         tick | head<<12 | env_done<<16 | winner<<24
     uint32_t *episode;    // [E]
     double *ret;          // [E*2]
-    unsigned long long *counters;  // [8]
+    unsigned long long *counters;  // [8] report counters + [1] episode-log cursor
     // Observation tables, built once per device by the host with the host libm -- the libm CPython's
     // math module calls -- and kept resident in the 126 MB L2 (DESIGN.md "Observation tables").
     const double *t360;   // [T_H][T_W]   360 - degrees(atan2(dy,dx) mod 2pi), battle_env.py:46-49
     const float *odt;     // [OD_H][OD_W] float32(sqrt(dx^2+dy^2)/diag*2-1),   battle_env.py:54-58,230
+    // Optional per-episode score log (main.py:219-221 score_dict): ring of {red score, blue score, code};
+    // code = 1 red won, 2 blue won, 3 tie, 6 both bases fell in the same tick.  counters[8] is its cursor.
+    float *ep_log;        // [ep_cap][3] or nullptr
+    long long ep_cap;
 };
 
 // Table geometry: every pair of on-field points (sprites.py:9-10) has dx in [-1200,1200], dy in [-800,800].
@@ -725,6 +729,13 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
         const int nt = __popc(__ballot_sync(FULL, ended && tie));
         const long long sr = warp_sum(ended ? __double2ll_rn(ret0 * 1048576.0) : 0ll);
         const long long sb = warp_sum(ended ? __double2ll_rn(ret1 * 1048576.0) : 0ll);
+#ifndef BS_NO_EPLOG
+        if (p.ep_log != nullptr && ended) {  // capacity is a power of two: no 64-bit division in the tick loop
+            const unsigned long long slot = atomicAdd(p.counters + 8, 1ull) & (unsigned long long)(p.ep_cap - 1);
+            p.ep_log[slot * 3 + 0] = (float)ret0; p.ep_log[slot * 3 + 1] = (float)ret1;
+            p.ep_log[slot * 3 + 2] = tie ? 3.0f : (red_won && blue_won ? 6.0f : (red_won ? 1.0f : 2.0f));
+        }
+#endif
         if (g.lane == 0) {
             if (nr) atomicAdd(p.counters + C_WINS_RED, (unsigned long long)nr);
             if (nb) atomicAdd(p.counters + C_WINS_BLUE, (unsigned long long)nb);

@@ -28,6 +28,7 @@
  *                                                         envs/battle_env.py:498-560, envs/sprites.py:155-178,265-278,353-360
  *   bs_stats             env.team[c]['wins'], ties, total_games + report sums
  *                                                         envs/battle_env.py:102-103,169-170; main.py:218-253
+ *   bs_episode_log       score_dict / scores.json history (row f3)     main.py:219-227
  *   bs_get_state/bs_set_state   (no reference equivalent: checkpoint + parity injection)
  *
  * Conventions
@@ -237,6 +238,14 @@ int bs_render(bs_handle *h, int64_t env, const bs_sprites *sprites, uint8_t *rgb
 /* out[8] = {red wins, blue wins, ties, total_games, sum(red episode return)*2^20,
  * sum(blue episode return)*2^20, env ticks, agent steps}; synchronises `stream`. */
 int bs_stats(bs_handle *h, int64_t out[8], void *stream);
+/* Per-episode score log (row f3; score_dict of main.py:219-221, scores.json): attach a DEVICE ring
+ * log [capacity][3] f32, capacity a power of two (NULL detaches).  Every game that ends in any kernel appends {red score,
+ * blue score, code} at (count mod capacity); code 1 = red won, 2 = blue won, 3 = tie, 6 = both bases
+ * fell in the same tick (winner 'blue', both wins counted, battle_env.py:363-372).  The order of
+ * games that end in the same launch is unspecified.  bs_episode_log_count synchronises `stream`. */
+int bs_episode_log(bs_handle *h, float *log, int64_t capacity);
+int bs_episode_log_count(bs_handle *h, int64_t *count, void *stream);
+
 /* Device address of the same 8 int64 counters (for an NCCL all-reduce without a host hop). */
 int bs_stats_device(bs_handle *h, int64_t **dev_counters);
 
