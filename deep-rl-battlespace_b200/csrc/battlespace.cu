@@ -78,6 +78,8 @@ struct StepArgs {
     bs_replay rp;         // optional: store_transition for act_team (capacity 0 = off)
     long long cursor_mod; // cursor % capacity
     int auto_reset;       // envs that finish in this tick are reset before the call returns
+    const float *obs_in;  // optional [E,2N,L]: the CURRENT observation of every env (what the previous step / reset
+                          // wrote): read instead of being recomputed before the tick
 };
 
 // Decode the lane's policy into (adisc, a[3], spread_u).  o = the lane's current observation
@@ -119,6 +121,9 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
     }
 }
 
+#ifndef STEP_HOIST_OBS
+#define STEP_HOIST_OBS 1
+#endif
 #ifndef STEP_MIN_BLOCKS
 #define STEP_MIN_BLOCKS 6
 #endif
@@ -129,6 +134,7 @@ __global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, 
     Geo<N> g(global_warp(), p.E);
     Lane<N> s;
     double ret0, ret1;
+
     load_lane(p, g, s, &rg, ret0, ret1);
 
     float o[L];
@@ -136,35 +142,47 @@ __global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, 
     long long row = 0;
     if (sa.rp.capacity > 0) row = (sa.cursor_mod + g.e % sa.rp.capacity) % sa.rp.capacity;
     const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT || sa.rp.capacity > 0;  // kernel-uniform
-    if (need_obs) { gather(g, s); observe<N>(p, s, o); }
+    if (need_obs && sa.obs_in != nullptr) {
+        const float *src = sa.obs_in + ((g.valid ? g.e : 0) * P + g.i) * L;
+#pragma unroll
+        for (int c = 0; c < L; ++c) o[c] = g.valid ? src[c] : -1.0f;
+    } else if (need_obs) { gather(g, s); observe<N>(p, s, o); }
     else {
 #pragma unroll
         for (int c = 0; c < L; ++c) o[c] = -1.0f;
     }
 
+    // external actions
+    const int pol = sa.pol[g.team];
+    const bool ext = g.valid && pol == POL_EXTERNAL && sa.dtype != ACT_NONE;
     int adisc = 0;
     double a[3] = {0, 0, 0}, spread_u = 0;
     float raw[4] = {0, 0, 0, 0};
-    const int pol = sa.pol[g.team];
+    if (ext) {
+        const long long idx = g.e * sa.act_agents + (sa.act_agents == P ? g.i : g.k);
+        if (!CONT) {
+            if (sa.dtype == ACT_I32) adisc = ((const int32_t *)sa.actions)[idx];
+            else {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) raw[c] = ((const float *)sa.actions)[idx * 4 + c];
+            }
+        } else if (sa.dtype == ACT_F32) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) a[c] = (double)((const float *)sa.actions)[idx * 3 + c];
+        } else {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) a[c] = ((const double *)sa.actions)[idx * 3 + c];
+        }
+    }
     if (g.valid) {
         const double *drow = sa.draws ? sa.draws + (g.e * P + g.i) * 5 : nullptr;
-        if (pol == POL_EXTERNAL && sa.dtype != ACT_NONE) {
-            const long long idx = g.e * sa.act_agents + (sa.act_agents == P ? g.i : g.k);
+        if (ext) {
             if (!CONT) {
-                if (sa.dtype == ACT_I32) {
-                    adisc = ((const int32_t *)sa.actions)[idx];
-                    if (adisc >= 0 && adisc < 4) raw[adisc] = 1.0f;
-                } else {
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) raw[c] = ((const float *)sa.actions)[idx * 4 + c];
-                    adisc = argmax4(raw);
-                }
-            } else if (sa.dtype == ACT_F32) {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) a[c] = clip1((double)((const float *)sa.actions)[idx * 3 + c]);
+                if (sa.dtype == ACT_I32) { if (adisc >= 0 && adisc < 4) raw[adisc] = 1.0f; }
+                else adisc = argmax4(raw);
             } else {
 #pragma unroll
-                for (int c = 0; c < 3; ++c) a[c] = clip1(((const double *)sa.actions)[idx * 3 + c]);
+                for (int c = 0; c < 3; ++c) a[c] = clip1(a[c]);
             }
             if (drow) spread_u = drow[4];
             else {
@@ -196,9 +214,26 @@ __global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, 
     }
     double rew;
     Tally tl;
-    tick<N, CONT>(p, g, s, rg, adisc, a, spread_u, rew, ret0, ret1, tl, sa.dtype == ACT_NONE);
-    if (sa.obs != nullptr || sa.rp.capacity > 0) {
-        observe<N>(p, s, o);
+    const bool want_obs = sa.obs != nullptr || sa.rp.capacity > 0;  // kernel-uniform
+    {
+        TickCtx c;
+        tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, sa.dtype == ACT_NONE, c);
+        // positions are final once the planes have moved: the table gathers of the new observation are
+        // issued before the bullet pass, which hides their L2 latency (42 % of this kernel's
+        // long-scoreboard stalls sat on them, profiles/r1j_step_team_*)
+        ObsLoads<N> q;
+#if STEP_HOIST_OBS
+        if (want_obs) { gather(g, s); observe_issue<N>(p, s, q); }
+#endif
+        unsigned ev; int died_ai;
+        bullets_ring<N>(g, s, rg, c, ev, died_ai);
+#if !STEP_HOIST_OBS
+        if (want_obs) observe_issue<N>(p, s, q);
+#endif
+        tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
+        if (want_obs) observe_finish<N>(s, q, o);
+    }
+    if (want_obs) {
         if (writer) {
             const long long ra_i = row * N + g.k;
             if (sa.rp.new_state) {
@@ -813,6 +848,7 @@ int bs_rollout_actor(bs_handle *h, int T, int learner_team, const bs_actor *acto
     DeviceGuard guard(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     StepArgs sa{act_scratch, BS_ACT_F32, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, nullptr, obs, rew, done, env_done, winner, {}, 0, 1};
+    sa.obs_in = obs;  // the buffer holds every env's current observation: no need to rebuild it before the tick
     sa.pol[1 - learner_team] = other_policy;
     if (replay && replay->capacity > 0) sa.rp = *replay;
     for (int t = 0; t < T; ++t) {
