@@ -42,15 +42,24 @@ __device__ __forceinline__ int argmax4(const float *v) {  // np.argmax: first ma
 template <int N>
 __global__ void __launch_bounds__(BLOCK) reset_kernel(Params p, const uint8_t *mask, const int32_t *draws, float *obs) {
     constexpr int P = 2 * N, L = 3 * N + 2;
-    __shared__ Ring rg;
-    Geo<N> g(global_warp(), p.E);
+    __shared__ WarpPool pools[BLOCK / 32];
+    WarpPool &w = pools[threadIdx.x >> 5];
+    const long long gw = global_warp();
+    Geo<N> g(gw, p.E);
     Lane<N> s;
     double ret0, ret1;
-    load_lane(p, g, s, &rg, ret0, ret1);
+    load_lane(p, g, s, ret0, ret1);
     const bool need = g.valid && (mask == nullptr || mask[g.e] != 0);
     if (need) {
-        reset_lane(p, g, s, &rg, draws != nullptr, draws ? draws + g.e * (4 + 6 * N) : nullptr);
+        reset_lane(p, g, s, draws != nullptr, draws ? draws + g.e * (4 + 6 * N) : nullptr);
         ret0 = ret1 = 0;
+    }
+    const unsigned killmask = __ballot_sync(FULL, need);
+    if (killmask) {  // self.bullets = [] for the envs that were reset, battle_env.py:272
+        int cnt;
+        pool_load(p, gw, gw < p.W, g.lane, w, cnt);
+        pool_filter(w, cnt, killmask, g.lane);
+        pool_store(p, gw, gw < p.W, g.lane, w, cnt);
     }
     gather(g, s);
     if (obs != nullptr) {
@@ -62,7 +71,7 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(Params p, const uint8_t *m
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
     }
-    if (need) store_lane(p, g, s, &rg, ret0, ret1, true);
+    if (need) store_lane(p, g, s, ret0, ret1, true);
 }
 
 struct StepArgs {
@@ -121,21 +130,22 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
     }
 }
 
-#ifndef STEP_HOIST_OBS
-#define STEP_HOIST_OBS 1
-#endif
 #ifndef STEP_MIN_BLOCKS
 #define STEP_MIN_BLOCKS 6
 #endif
 template <int N, bool CONT>
 __global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, StepArgs sa) {
     constexpr int P = 2 * N, L = 3 * N + 2;
-    __shared__ Ring rg;
-    Geo<N> g(global_warp(), p.E);
+    __shared__ WarpPool pools[BLOCK / 32];
+    WarpPool &w = pools[threadIdx.x >> 5];
+    const long long gw = global_warp();
+    Geo<N> g(gw, p.E);
     Lane<N> s;
     double ret0, ret1;
-
-    load_lane(p, g, s, &rg, ret0, ret1);
+    load_lane(p, g, s, ret0, ret1);
+    int cnt;
+    pool_load(p, gw, gw < p.W, g.lane, w, cnt);
+    pool_publish_base<N>(g, s, w);
 
     float o[L];
     const bool writer = g.valid && sa.rp.capacity > 0 && g.team == sa.act_team;
@@ -222,14 +232,10 @@ __global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, 
         // issued before the bullet pass, which hides their L2 latency (42 % of this kernel's
         // long-scoreboard stalls sat on them, profiles/r1j_step_team_*)
         ObsLoads<N> q;
-#if STEP_HOIST_OBS
-        if (want_obs) { gather(g, s); observe_issue<N>(p, s, q); }
-#endif
-        unsigned ev; int died_ai;
-        bullets_ring<N>(g, s, rg, c, ev, died_ai);
-#if !STEP_HOIST_OBS
+        gather(g, s);  // enemy positions after the move, hp before the bullet loop
         if (want_obs) observe_issue<N>(p, s, q);
-#endif
+        unsigned ev; int died_ai;
+        bullets_dense<N>(g, s, w, cnt, c, false, ev, died_ai);
         tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
         if (want_obs) observe_finish<N>(s, q, o);
     }
@@ -257,7 +263,8 @@ __global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, 
     const bool fresh = sa.auto_reset && g.valid && s.env_done;
     const int out_done = s.env_done, out_hp = s.hp, out_winner = s.winner;
     if (sa.auto_reset && __any_sync(FULL, fresh)) {
-        if (fresh) { reset_lane(p, g, s, &rg, false, nullptr); ret0 = ret1 = 0; }
+        if (fresh) { reset_lane(p, g, s, false, nullptr); ret0 = ret1 = 0; }
+        pool_filter(w, cnt, __ballot_sync(FULL, fresh), g.lane);  // the finished games' bullets vanish, battle_env.py:272
         gather(g, s);
         float o2[L];
         observe<N>(p, s, o2);
@@ -276,7 +283,8 @@ __global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, 
             if (sa.winner) sa.winner[g.e] = (int8_t)out_winner;
         }
     }
-    store_lane(p, g, s, &rg, ret0, ret1, sa.auto_reset != 0);
+    store_lane(p, g, s, ret0, ret1, sa.auto_reset != 0);
+    pool_store(p, gw, gw < p.W, g.lane, w, cnt);
     flush_tally<N>(p, tl);
 }
 
@@ -306,9 +314,9 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
     Geo<N> g(global_warp(), ra.e_end, ra.e0);
     Lane<N> s;
     double ret0, ret1;
-    load_lane(p, g, s, nullptr, ret0, ret1);
+    load_lane(p, g, s, ret0, ret1);
     int cnt;
-    pool_load<N>(p, g, s, w, cnt);
+    pool_load(p, ra.e0 / Geo<N>::K + global_warp(), ra.e0 + global_warp() * Geo<N>::K < ra.e_end, g.lane, w, cnt);  // chunks start on a warp boundary
     pool_publish_base<N>(g, s, w);
     gather(g, s);
     float o[L];
@@ -324,7 +332,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
         // auto-reset: the game loop's env.reset() -- main.py:148
         const bool need = g.valid && s.env_done;
         if (__any_sync(FULL, need)) {
-            if (need) { reset_lane(p, g, s, nullptr, false, nullptr); ret0 = ret1 = 0; pool_publish_base<N>(g, s, w); }
+            if (need) { reset_lane(p, g, s, false, nullptr); ret0 = ret1 = 0; pool_publish_base<N>(g, s, w); }
             gather(g, s);
             float o2[L];
             observe<N>(p, s, o2);
@@ -370,6 +378,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
             TickCtx c;
             tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, false, c);
             unsigned ev; int died_ai;
+            gather(g, s);  // enemy positions after the move, hp before the bullet loop
             bullets_dense<N>(g, s, w, cnt, c, need, ev, died_ai);
             ObsLoads<N> q;
             observe_issue<N>(p, s, q);  // positions are final; hp / alive masks are settled by then
@@ -389,8 +398,8 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
         row += ra.e_mod;
         if (row >= ra.rp.capacity) row -= ra.rp.capacity;
     }
-    store_lane(p, g, s, nullptr, ret0, ret1, true);
-    pool_store<N>(p, g, s, w, cnt);
+    store_lane(p, g, s, ret0, ret1, true);
+    pool_store(p, ra.e0 / Geo<N>::K + global_warp(), ra.e0 + global_warp() * Geo<N>::K < ra.e_end, g.lane, w, cnt);
     flush_tally<N>(p, tl);
 }
 
@@ -481,9 +490,9 @@ struct ObsTables { double *t360 = nullptr; float *odt = nullptr; size_t bytes = 
 
 struct bs_handle {
     bs_config cfg;
-    int N, P, L, A;
+    int N, P, L, A, K;
     bool cont;
-    int64_t E;
+    int64_t E, W;
     int device;
     Params p;
     ObsTables tables;
@@ -680,10 +689,12 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     p.diag = std::sqrt(std::pow(1200.0, 2) + std::pow(800.0, 2));
     if (p.diag != DIAG) { delete h; return fail(BS_E_INVALID, "host sqrt(1200^2+800^2) differs from the device constant"); }
     const size_t EP = (size_t)n_envs * h->P;
+    h->K = 32 / h->P; h->W = (n_envs + h->K - 1) / h->K;  // envs per warp, warps
+    h->p.W = h->W;
     int rc;
     if ((rc = dalloc(h, &p.plane_pos, EP)) || (rc = dalloc(h, &p.plane_dir, EP)) || (rc = dalloc(h, &p.plane_hp, EP)) ||
         (rc = dalloc(h, &p.base_pos, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.base_hp, (size_t)n_envs * 2)) ||
-        (rc = dalloc(h, &p.bul_pos, EP * SLOTS)) || (rc = dalloc(h, &p.bul_dlt, EP * SLOTS)) ||
+        (rc = dalloc(h, &p.pool, (size_t)h->W * POOL_CAP)) || (rc = dalloc(h, &p.pool_cnt, (size_t)h->W)) ||
         (rc = dalloc(h, &p.meta, (size_t)n_envs)) || (rc = dalloc(h, &p.episode, (size_t)n_envs)) ||
         (rc = dalloc(h, &p.ret, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.counters, 9))) {
         bs_destroy(h);
@@ -930,8 +941,9 @@ int bs_get_state(bs_handle *h, const bs_state_view *v) {
     DeviceGuard guard(h->device);
     CU(cudaDeviceSynchronize());
     const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
-    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), epi((size_t)E), bp(EP * SLOTS);
-    std::vector<int32_t> bd(EP * SLOTS);
+    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), epi((size_t)E);
+    std::vector<uint2> pool((size_t)h->W * POOL_CAP);
+    std::vector<int> pcnt((size_t)h->W);
     std::vector<double> dir(EP), ret((size_t)E * 2);
     std::vector<int8_t> hp(EP);
     std::vector<int16_t> bhp((size_t)E * 2);
@@ -941,36 +953,44 @@ int bs_get_state(bs_handle *h, const bs_state_view *v) {
     CU(cudaMemcpy(hp.data(), p.plane_hp, EP, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(bpos.data(), p.base_pos, (size_t)E * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(bhp.data(), p.base_hp, (size_t)E * 4, cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(bp.data(), p.bul_pos, EP * SLOTS * 4, cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(bd.data(), p.bul_dlt, EP * SLOTS * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(pool.data(), p.pool, pool.size() * sizeof(uint2), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(pcnt.data(), p.pool_cnt, pcnt.size() * sizeof(int), cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(meta.data(), p.meta, (size_t)E * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(epi.data(), p.episode, (size_t)E * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(ret.data(), p.ret, (size_t)E * 16, cudaMemcpyDeviceToHost));
-    // ring slot -> age: the newest bullet (age 1) sits in slot head; exported index = age - 1
     for (size_t a = 0; a < EP; ++a) {
         if (v->plane_x) v->plane_x[a] = (int16_t)(pos[a] & 0xffff);
         if (v->plane_y) v->plane_y[a] = (int16_t)(pos[a] >> 16);
         if (v->plane_dir) v->plane_dir[a] = dir[a];
         if (v->plane_hp) v->plane_hp[a] = hp[a];
-        const int head = (int)((meta[a / P] >> 12) & 0xf);
-        for (int q = 0; q < SLOTS; ++q) {
-            const uint32_t ps = bp[(size_t)q * EP + a];
-            const int32_t dl = bd[(size_t)q * EP + a];
-            const bool valid = (ps & B_VALID) != 0;
-            const int o = (head - q + SLOTS) % SLOTS;
+        for (int o = 0; o < SLOTS; ++o) {
+            if (v->bullet_pos) { v->bullet_pos[(a * SLOTS + o) * 2] = -1; v->bullet_pos[(a * SLOTS + o) * 2 + 1] = -1; }
+            if (v->bullet_vel) { int8_t *vel = v->bullet_vel + (a * SLOTS + o) * 3; vel[0] = vel[1] = vel[2] = 0; }
+        }
+    }
+    // pool entry -> (env, plane, age): owner lane = sub * 2N + plane, env = warp * K + sub; exported index = age - 1
+    for (int64_t wv = 0; wv < h->W; ++wv)
+        for (int q = 0; q < pcnt[wv]; ++q) {
+            const uint2 en = pool[(size_t)wv * POOL_CAP + q];
+            const uint32_t ps = en.x, M = en.y;
+            if (!(ps & B_VALID)) continue;
+            const int owner = (M >> 23) & 31, age = (int)(M >> 28), sub = owner / P, i = owner - sub * P;
+            const int64_t e = wv * h->K + sub;
+            if (e >= E || age < 1 || age > SLOTS) continue;
+            const size_t a = (size_t)e * P + i;
+            const int o = age - 1;
+            const int32_t dl = meta_dlt(M);
             if (v->bullet_pos) {
-                v->bullet_pos[(a * SLOTS + o) * 2] = valid ? (int16_t)((int)(ps & 0xffff) - 64) : (int16_t)-1;
-                v->bullet_pos[(a * SLOTS + o) * 2 + 1] = valid ? (int16_t)((int)((ps >> 16) & 0x1fff) - 64) : (int16_t)-1;
+                v->bullet_pos[(a * SLOTS + o) * 2] = (int16_t)((int)(ps & 0xffff) - 64);
+                v->bullet_pos[(a * SLOTS + o) * 2 + 1] = (int16_t)((int)((ps >> 16) & 0x1fff) - 64);
             }
             if (v->bullet_vel) {
                 const int sx = (int16_t)(dl & 0xffff), sy = (dl - sx) >> 16;
-                v->bullet_vel[(a * SLOTS + o) * 3] = valid ? (int8_t)sx : (int8_t)0;
-                v->bullet_vel[(a * SLOTS + o) * 3 + 1] = valid ? (int8_t)sy : (int8_t)0;
-                v->bullet_vel[(a * SLOTS + o) * 3 + 2] =
-                    valid ? (int8_t)(1 | ((ps & B_XEXACT) ? 2 : 0) | ((ps & B_YEXACT) ? 4 : 0)) : (int8_t)0;
+                v->bullet_vel[(a * SLOTS + o) * 3] = (int8_t)sx;
+                v->bullet_vel[(a * SLOTS + o) * 3 + 1] = (int8_t)sy;
+                v->bullet_vel[(a * SLOTS + o) * 3 + 2] = (int8_t)(1 | ((ps & B_XEXACT) ? 2 : 0) | ((ps & B_YEXACT) ? 4 : 0));
             }
         }
-    }
     for (int64_t e = 0; e < E; ++e) {
         for (int t = 0; t < 2; ++t) {
             if (v->base_pos) { v->base_pos[(e * 2 + t) * 2] = (int16_t)(bpos[e * 2 + t] & 0xffff); v->base_pos[(e * 2 + t) * 2 + 1] = (int16_t)(bpos[e * 2 + t] >> 16); }
@@ -993,9 +1013,9 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     DeviceGuard guard(h->device);
     CU(cudaDeviceSynchronize());
     const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
-    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), bp(EP * SLOTS);
-    std::vector<int32_t> bd(EP * SLOTS);
-    std::vector<int8_t> hp(EP);
+    std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E);
+    std::vector<uint2> pool((size_t)h->W * POOL_CAP);
+    std::vector<int> pcnt((size_t)h->W, 0);
     // the observation tables (and the packed 11/10-bit plane words) cover on-field points only
     for (size_t a = 0; a < EP; ++a)
         if (v->plane_x[a] < 0 || v->plane_x[a] > 1200 || v->plane_y[a] < 0 || v->plane_y[a] > 800)
@@ -1003,26 +1023,28 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     for (size_t q = 0; q < (size_t)E * 2; ++q)
         if (v->base_pos[q * 2] < 0 || v->base_pos[q * 2] > 1200 || v->base_pos[q * 2 + 1] < 0 || v->base_pos[q * 2 + 1] > 800)
             return fail(BS_E_INVALID, "bs_set_state: base position outside the 1200x800 field");
-    // age -> ring slot with head = tick mod 12 (any head works as long as the slots agree with it)
-    for (size_t a = 0; a < EP; ++a) {
-        pos[a] = (uint32_t)(uint16_t)v->plane_x[a] | ((uint32_t)(uint16_t)v->plane_y[a] << 16);
-        const int head = (int)(v->tick[a / P] % SLOTS);
-        for (int o = 0; o < SLOTS; ++o) {
-            const int8_t *vel = v->bullet_vel + (a * SLOTS + o) * 3;
-            const int16_t *ps = v->bullet_pos + (a * SLOTS + o) * 2;
-            const bool valid = (vel[2] & 1) != 0 && o < SLOTS - 1;  // age 12 never survives a tick
-            const int q = (head - o + SLOTS) % SLOTS;
-            bp[(size_t)q * EP + a] = valid ? ((((uint32_t)(ps[0] + 64)) | ((uint32_t)(ps[1] + 64) << 16)) | B_VALID |
-                                              ((vel[2] & 2) ? B_XEXACT : 0u) | ((vel[2] & 4) ? B_YEXACT : 0u))
-                                           : 0u;
-            bd[(size_t)q * EP + a] = valid ? ((int32_t)vel[0] + (int32_t)vel[1] * 65536) : 0;
-        }
-    }
+    for (size_t a = 0; a < EP; ++a) pos[a] = (uint32_t)(uint16_t)v->plane_x[a] | ((uint32_t)(uint16_t)v->plane_y[a] << 16);
+    // bullets -> the warp pools, oldest first (the order inside a pool carries no meaning)
+    for (int64_t wv = 0; wv < h->W; ++wv)
+        for (int o = SLOTS - 2; o >= 0; --o)          // age 12 never survives a tick
+            for (int owner = 0; owner < h->K * P; ++owner) {
+                const int sub = owner / P, i = owner - sub * P;
+                const int64_t e = wv * h->K + sub;
+                if (e >= E) continue;
+                const size_t a = (size_t)e * P + i;
+                const int8_t *vel = v->bullet_vel + (a * SLOTS + o) * 3;
+                const int16_t *ps = v->bullet_pos + (a * SLOTS + o) * 2;
+                if (!(vel[2] & 1)) continue;
+                const uint32_t Pw = (((uint32_t)(ps[0] + 64)) | ((uint32_t)(ps[1] + 64) << 16)) | B_VALID |
+                                    ((vel[2] & 2) ? B_XEXACT : 0u) | ((vel[2] & 4) ? B_YEXACT : 0u);
+                const int32_t dl = (int32_t)vel[0] + (int32_t)vel[1] * 65536;
+                const uint32_t M = ((uint32_t)dl & 0x7fffffu) | ((uint32_t)owner << 23) | ((uint32_t)(o + 1) << 28);
+                pool[(size_t)wv * POOL_CAP + pcnt[wv]++] = make_uint2(Pw, M);
+            }
     for (int64_t e = 0; e < E; ++e) {
         for (int t = 0; t < 2; ++t)
             bpos[e * 2 + t] = (uint32_t)(uint16_t)v->base_pos[(e * 2 + t) * 2] | ((uint32_t)(uint16_t)v->base_pos[(e * 2 + t) * 2 + 1] << 16);
-        meta[e] = ((uint32_t)v->tick[e] & 0xfff) | ((uint32_t)(v->tick[e] % SLOTS) << 12) |
-                  ((uint32_t)(v->env_done[e] ? 1 : 0) << 16) | ((uint32_t)(uint8_t)v->winner[e] << 24);
+        meta[e] = ((uint32_t)v->tick[e] & 0xfff) | ((uint32_t)(v->env_done[e] ? 1 : 0) << 16) | ((uint32_t)(uint8_t)v->winner[e] << 24);
     }
     const Params &p = h->p;
     CU(cudaMemcpy(p.plane_pos, pos.data(), EP * 4, cudaMemcpyHostToDevice));
@@ -1030,8 +1052,8 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     CU(cudaMemcpy(p.plane_hp, v->plane_hp, EP, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.base_pos, bpos.data(), (size_t)E * 8, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.base_hp, v->base_hp, (size_t)E * 4, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(p.bul_pos, bp.data(), EP * SLOTS * 4, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(p.bul_dlt, bd.data(), EP * SLOTS * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.pool, pool.data(), pool.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p.pool_cnt, pcnt.data(), pcnt.size() * sizeof(int), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.meta, meta.data(), (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.episode, v->episode, (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.ret, v->team_return, (size_t)E * 16, cudaMemcpyHostToDevice));

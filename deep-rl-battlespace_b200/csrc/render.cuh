@@ -69,20 +69,25 @@ __global__ void __launch_bounds__(256) render_kernel(Params p, RenderArgs ra) {
     __shared__ RObj obj[MAXO];
     __shared__ RBar bar[P + 2];
     __shared__ int base_xy[2][2];
-    __shared__ int n_bul, n_obj;
-    const long long e = ra.env, EP = p.E * P;
-    if (threadIdx.x == 0) { n_bul = 0; n_obj = 0; }
-    __syncthreads();
+    const long long e = ra.env;
     // ---- stage the env's objects: bullets first (drawn first), then planes -----------------------
-    for (int q = threadIdx.x; q < P * SLOTS; q += blockDim.x) {
-        // list order of self.bullets is spawn order; any fixed order gives the same picture unless two
-        // bullets overlap, so the order here is simply (age oldest first, agent) like the tick
-        const int ai = q / P, i = q - ai * P;
-        const uint32_t m = p.meta[e];
-        int slot = (int)((m >> 12) & 0xf) + 1 + ai; if (slot >= SLOTS) slot -= SLOTS;
-        const uint32_t Pw = p.bul_pos[slot * EP + e * P + i];
-        if (Pw & B_VALID) {
-            const int32_t D = p.bul_dlt[slot * EP + e * P + i];
+    for (int q = threadIdx.x; q < P * SLOTS; q += blockDim.x) obj[q].kind = -1;
+    __syncthreads();
+    {
+        // the env's bullets are the entries of its warp's pool whose owner lane belongs to it; they are
+        // staged at [age index][agent] -- list order of self.bullets is spawn order, and any fixed order
+        // gives the same picture unless two bullets of different teams overlap
+        constexpr int K = 32 / P;
+        const long long gw = e / K;
+        const int lane0 = (int)(e - gw * K) * P;
+        const int cnt = p.pool_cnt[gw];
+        for (int q = threadIdx.x; q < cnt; q += blockDim.x) {
+            const uint2 en = p.pool[gw * POOL_CAP + q];
+            const uint32_t Pw = en.x, M = en.y;
+            const int owner = (M >> 23) & 31, age = (int)(M >> 28);
+            if (!(Pw & B_VALID) || owner < lane0 || owner >= lane0 + P || age < 1 || age > SLOTS) continue;
+            const int i = owner - lane0, ai = SLOTS - age;
+            const int32_t D = meta_dlt(M);
             int sx = (int16_t)(D & 0xffff), sy = (D - sx) >> 16;
             const uint32_t Qw = (Pw & B_POS) - B_BIAS;
             const double len = sqrt((double)(sx * sx + sy * sy));
@@ -93,9 +98,6 @@ __global__ void __launch_bounds__(256) render_kernel(Params p, RenderArgs ra) {
             o.s = len > 0 ? (int)rint((double)-sy / len * (1 << Q)) : 0;
             o.w = BUL_W; o.h = BUL_H; o.rad2 = 8; o.kind = 2 + (i >= N);
             obj[ai * P + i] = o;
-            atomicAdd(&n_bul, 1);
-        } else {
-            obj[ai * P + i].kind = -1;
         }
     }
     for (int i = threadIdx.x; i < P; i += blockDim.x) {

@@ -1,11 +1,12 @@
 // tick.cuh -- device-side Battlespace tick for sm_100a.
 //
 // Mapping: one LANE per plane, one env per group of G = 2N consecutive lanes (red planes first),
-// K = 32 / G envs per warp.  A lane keeps its own plane in registers, a replicated view of the
-// enemy team (refreshed with warp shuffles) and its own 12 bullets in a shared-memory ring
-// (slot = spawn tick mod 12, one column per thread: bank-conflict free and dynamically indexable,
-// so the bullet loop stays ROLLED -- the first version of this file unrolled it over registers and
-// ran out of instruction cache: 132 KB of SASS per tick, stall_no_inst 55 %, profiles/r1_*).
+// K = 32 / G envs per warp.  A lane keeps its own plane in registers and a replicated view of the
+// enemy team (refreshed with warp shuffles); the warp's live bullets sit PACKED in a per-warp pool --
+// in shared memory while a kernel runs, in HBM between launches (same layout, copied coalesced) -- so
+// any lane advances any bullet and every kernel shares one bullet pass.  (History: v1 unrolled a
+// 12-slot register ring: 132 KB of SASS per tick, stall_no_inst 55 %; v2 kept a per-lane ring in shared
+// memory and HBM: only ~1/4 of the slots hold a bullet, the loop ran at 8 of 32 lanes; profiles/r1_*.)
 // Control flow that contains a shuffle is warp-uniform; per-env conditions are predicates.
 //
 // Arithmetic follows the reference operation by operation in IEEE double (compiled with
@@ -38,6 +39,7 @@ enum { C_WINS_RED = 0, C_WINS_BLUE, C_TIES, C_GAMES, C_RET_RED, C_RET_BLUE, C_TI
 
 struct Params {
     long long E;          // envs in this handle
+    long long W;          // warps = ceil(E / K), K = 32 / 2N envs per warp
     long long env_offset; // global index of env 0 (sharding)
     uint32_t seed_lo, seed_hi;
     int tie_tick;         // first step call whose accumulated 0.1s reach 10+2N (battle_env.py:316-319)
@@ -49,9 +51,9 @@ struct Params {
     int8_t *plane_hp;     // [E*2N]
     uint32_t *base_pos;   // [E*2]       x | y<<16
     int16_t *base_hp;     // [E*2]
-    uint32_t *bul_pos;    // [12][E*2N]  ring slot-major (coalesced per slot); word layout above
-    int32_t *bul_dlt;     // [12][E*2N]
-    uint32_t *meta;       // [E]         tick | head<<12 | env_done<<16 | winner<<24
+    uint2 *pool;          // [W][POOL_CAP] W = ceil(E/K) warps: the warp's bullets, packed (x = pos word, y = meta word)
+    int *pool_cnt;        // [W]         entries in use (dead entries are squeezed out by the next pass)
+    uint32_t *meta;       // [E]         tick | env_done<<16 | winner<<24
     uint32_t *episode;    // [E]
     double *ret;          // [E*2]
     unsigned long long *counters;  // [8] report counters + [1] episode-log cursor
@@ -68,12 +70,6 @@ struct Params {
 // Table geometry: every pair of on-field points (sprites.py:9-10) has dx in [-1200,1200], dy in [-800,800].
 constexpr int T_DX = 1200, T_DY = 800, T_W = 2 * T_DX + 1, T_H = 2 * T_DY + 1;
 constexpr int OD_W = T_DX + 1, OD_H = T_DY + 1;
-
-// The block's bullet ring in shared memory: [slot][thread].
-struct Ring {
-    uint32_t pos[SLOTS][BLOCK];
-    int32_t dlt[SLOTS][BLOCK];
-};
 
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al. 2011); counter layout in include/battlespace.h
@@ -158,7 +154,6 @@ struct Lane {
     int ebx, eby;           // enemy base centre
     int bhp_own, bhp_enemy; // base hit points (replicated over the group)
     int tick, env_done, winner;
-    int head;               // ring slot of the newest bullet (advances on every tick that moves bullets)
     uint32_t episode;
     // replicated view of the enemy team, refreshed by gather()
     uint32_t exy[N];        // x | y << 16
@@ -402,7 +397,6 @@ __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lan
     s.tick += adv ? 1 : 0;                                              // :316
     c.time_tie = adv && s.tick >= p.tie_tick;                           // :319-323
     c.run = adv && !c.time_tie;
-    if (c.run) s.head = s.head == SLOTS - 1 ? 0 : s.head + 1;
 
     // ---- actions of the planes that are alive, :325-329 + process_action :383-424 -----------
     const int x0 = s.x, y0 = s.y;
@@ -499,43 +493,13 @@ __device__ __forceinline__ void resolve_plane_hits(const Geo<N> &g, Lane<N> &s, 
     }
 }
 
-// Bullets in the per-lane ring -- :332-360, sprites.py:321-351.  Oldest first; same age: agent order.
-// Phase 1 (no ordering needed): move every bullet, settle misses and base hits, and flag the
-// bullets that overlap an enemy plane alive at the start of the loop.  ev: 2 bits per age
-// index ai (0 = oldest): 1 miss, 2 base hit, 3 plane hit.
-template <int N>
-__device__ __forceinline__ void bullets_ring(const Geo<N> &g, Lane<N> &s, Ring &rg, const TickCtx &c,
-                                             unsigned &ev, int &died_ai) {
-    const int tid = threadIdx.x;
-    const int h = s.head;
-    const bool run = c.run;
-    if (run) { rg.pos[h][tid] = c.spawnP; rg.dlt[h][tid] = c.spawnD; }
-    gather(g, s);  // enemy positions after the move, hp before the bullet loop
-    unsigned cand = 0;
-    ev = 0; died_ai = -1;
-    const uint32_t baseT = (((uint32_t)(s.ebx - 33)) | ((uint32_t)(s.eby - 32) << 16)) + B_BIAS;
-    int slot = h;
-#pragma unroll 1
-    for (int ai = 0; ai < SLOTS; ++ai) {
-        slot = slot + 1 == SLOTS ? 0 : slot + 1;
-        uint32_t P = rg.pos[slot][tid];
-        if (run && (P & B_VALID)) {
-            if (bullet_advance(P, rg.dlt[slot][tid], SLOTS - ai)) { ev |= 1u << (2 * ai); P = 0; }
-            else if (rect_hit((P & B_POS) - baseT, 67u, 64u)) { ev |= 2u << (2 * ai); P = 0; }
-            else if (plane_overlaps<N>(s, P) & s.am) cand |= 1u << ai;
-            rg.pos[slot][tid] = P;
-        }
-    }
-    resolve_plane_hits<N>(g, s, cand, ev, died_ai,
-        [&](int ai) { int sl = h + 1 + ai; if (sl >= SLOTS) sl -= SLOTS; return plane_overlaps<N>(s, rg.pos[sl][tid]); },
-        [&](int ai) { int sl = h + 1 + ai; if (sl >= SLOTS) sl -= SLOTS; rg.pos[sl][tid] = 0; });
-}
-
-// ---- bullets in a dense per-warp pool (fused rollout) ---------------------------------------------
-// In the ring only ~1/4 of the slots hold a bullet, so a lane-per-owner loop over 12 slots runs at
-// ~8 of 32 lanes (profiles/r1c_*).  The rollout kernel therefore keeps the warp's live bullets
-// packed in shared memory, any lane updates any bullet, and results travel back to the owner lane
-// as bits keyed by (owner, age) -- which is all the ordered part of the loop needs.
+// ---- bullets in a dense per-warp pool -- battle_env.py:332-360, sprites.py:321-351 -----------------
+// With one 12-slot ring per lane only ~1/4 of the slots hold a bullet, so a lane-per-owner loop runs
+// at ~8 of 32 lanes (profiles/r1c_*).  The warp's live bullets are therefore kept packed, any lane
+// updates any bullet, and results travel back to the owner lane as bits keyed by (owner, age) --
+// which is all the ordered part of the loop needs.  Phase 1 (order free): move every bullet, settle
+// misses and base hits, flag overlaps with enemy planes alive at the start of the loop; phase 2:
+// resolve_plane_hits.  ev: 2 bits per age index ai (0 = oldest): 1 miss, 2 base hit, 3 plane hit.
 //   pos  : as in the ring (0 = dead entry, squeezed out by the next pass)
 //   meta : (sx + sy*65536) in bits 0..22 (two's complement) | owner lane << 23 | updates done << 28
 constexpr int WARPS = BLOCK / 32;
@@ -551,7 +515,7 @@ struct WarpPool {
 __device__ __forceinline__ uint32_t pack_meta(int32_t dlt, int owner, int age) {
     return ((uint32_t)dlt & 0x7fffffu) | ((uint32_t)owner << 23) | ((uint32_t)age << 28);
 }
-__device__ __forceinline__ int32_t meta_dlt(uint32_t m) { return (int32_t)(m << 9) >> 9; }
+__host__ __device__ __forceinline__ int32_t meta_dlt(uint32_t m) { return (int32_t)(m << 9) >> 9; }
 
 template <int N>
 __device__ __forceinline__ void pool_publish_base(const Geo<N> &g, const Lane<N> &s, WarpPool &w) {
@@ -574,7 +538,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
     }
     const int cnt_in = cnt + __popc(sp);
     __syncwarp();
-    gather(g, s);  // enemy positions after the move, hp before the bullet loop
+    // (the caller has run gather(): enemy positions after the move, hp before the bullet loop)
     int out = 0;
 #pragma unroll 1
     for (int base = 0; base < cnt_in; base += 32) {
@@ -625,50 +589,44 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         [&](int ai) { w.pos[w.candt[ai][lane] >> 8] = 0; });
 }
 
-// ring (HBM state format) -> pool at the start of a launch: oldest age first
-template <int N>
-__device__ __forceinline__ void pool_load(const Params &p, const Geo<N> &g, const Lane<N> &s, WarpPool &w, int &cnt) {
-    const int lane = g.lane;
-    const unsigned lt = (1u << lane) - 1u;
-    const long long a = g.e * (2 * N) + g.i, EP = p.E * (2 * N);
-    cnt = 0;
+// HBM <-> shared memory: the pool has the same layout in both, so a launch copies `cnt` packed entries
+// (coalesced 8-byte words), not 24 ring words per lane.  gw = global warp index = first env / K.
+// wvalid: the warp owns envs of this launch (the last block's spare warps, and in a chunked launch the
+// warps past the chunk, must neither read nor write a pool).
+__device__ __forceinline__ void pool_load(const Params &p, long long gw, bool wvalid, int lane, WarpPool &w, int &cnt) {
+    cnt = wvalid ? p.pool_cnt[gw] : 0;
+    const uint2 *src = p.pool + gw * POOL_CAP;
+    for (int idx = lane; idx < cnt; idx += 32) { const uint2 v = src[idx]; w.pos[idx] = v.x; w.meta[idx] = v.y; }
     w.ev[lane] = 0; w.cand[lane] = 0;
-#pragma unroll 1
-    for (int o = SLOTS - 2; o >= 0; --o) {  // exported index o = updates done - 1 (bs_get_state)
-        int q = s.head - o; if (q < 0) q += SLOTS;
-        uint32_t P = 0; int32_t D = 0;
-        if (g.valid) { P = p.bul_pos[q * EP + a]; D = p.bul_dlt[q * EP + a]; }
-        const bool v = (P & B_VALID) != 0;
-        const unsigned b = __ballot_sync(FULL, v);
-        if (v) { const int idx = cnt + __popc(b & lt); w.pos[idx] = P; w.meta[idx] = pack_meta(D, lane, o + 1); }
-        cnt += __popc(b);
-    }
     __syncwarp();
 }
 
-// pool -> ring at the end of a launch
-template <int N>
-__device__ __forceinline__ void pool_store(const Params &p, const Geo<N> &g, const Lane<N> &s, WarpPool &w, int cnt) {
-    const int lane = g.lane;
-    const long long EP = p.E * (2 * N);
-    const long long a0 = (g.e * (2 * N) + g.i) - lane;  // agent index of lane 0 (lanes map to consecutive agents)
-    if (g.valid) {
-#pragma unroll
-        for (int q = 0; q < SLOTS; ++q) { p.bul_pos[q * EP + a0 + lane] = 0; p.bul_dlt[q * EP + a0 + lane] = 0; }
-    }
-    w.ev[lane] = (uint32_t)s.head;
+__device__ __forceinline__ void pool_store(const Params &p, long long gw, bool wvalid, int lane, const WarpPool &w, int cnt) {
     __syncwarp();
-    const long long a00 = __shfl_sync(FULL, a0, 0);  // lane 0 is always a valid lane of a launched warp
+    if (!wvalid) return;
+    uint2 *dst = p.pool + gw * POOL_CAP;
+    for (int idx = lane; idx < cnt; idx += 32) dst[idx] = make_uint2(w.pos[idx], w.meta[idx]);
+    if (lane == 0) p.pool_cnt[gw] = cnt;
+}
+
+// Drops the bullets of the lanes in `killmask` (their envs were reset: self.bullets = [], battle_env.py:272)
+// and squeezes dead entries out, in place.
+__device__ __forceinline__ void pool_filter(WarpPool &w, int &cnt, unsigned killmask, int lane) {
+    const unsigned lt = (1u << lane) - 1u;
+    __syncwarp();
+    int out = 0;
 #pragma unroll 1
-    for (int idx = lane; idx < cnt; idx += 32) {
-        const uint32_t P = w.pos[idx], M = w.meta[idx];
-        if (P & B_VALID) {
-            const int owner = (M >> 23) & 31, age = M >> 28;
-            int q = (int)w.ev[owner] - (age - 1); if (q < 0) q += SLOTS;
-            p.bul_pos[q * EP + a00 + owner] = P;
-            p.bul_dlt[q * EP + a00 + owner] = meta_dlt(M);
-        }
+    for (int base = 0; base < cnt; base += 32) {
+        const int idx = base + lane;
+        uint32_t P = 0, M = 0;
+        if (idx < cnt) { P = w.pos[idx]; M = w.meta[idx]; }
+        const bool keep = (P & B_VALID) != 0 && !((killmask >> ((M >> 23) & 31)) & 1u);
+        const unsigned kb = __ballot_sync(FULL, keep);
+        if (keep) { const int n = out + __popc(kb & lt); w.pos[n] = P; w.meta[n] = M; }  // n <= idx: never ahead of a read
+        out += __popc(kb);
     }
+    cnt = out;
+    __syncwarp();
 }
 
 //   rew : this lane's reward for the tick (double, reference accumulation order).
@@ -747,23 +705,10 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
     }
 }
 
-// The single-tick form used by step_kernel.  On return s holds the new state and gather() data is
-// current (positions after the move, enemy hp after the bullet loop), so observe() can follow.
-template <int N, bool CONT>
-__device__ __forceinline__ void tick(const Params &p, const Geo<N> &g, Lane<N> &s, Ring &rg, int adisc,
-                                     const double (&a)[3], double spread_u, double &rew,
-                                     double &ret0, double &ret1, Tally &tl, bool no_actions = false) {
-    TickCtx c;
-    tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, no_actions, c);
-    unsigned ev; int died_ai;
-    bullets_ring<N>(g, s, rg, c, ev, died_ai);
-    tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
-}
-
 // parallel_env.reset for one lane -- battle_env.py:246-279, sprites.py:74-91,238-252.
 // d_* are this lane's spawn values when injected (inj=true), else Philox.
 template <int N>
-__device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lane<N> &s, Ring *rg, bool inj,
+__device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lane<N> &s, bool inj,
                                            const int32_t *draws /* this env's [4+6N] or null */) {
     s.episode += 1;
     int rbx, rby, bbx, bby, px, py, pd;
@@ -784,30 +729,17 @@ __device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lan
     s.x = px; s.y = py; s.dir = (double)pd; s.hp = 4;                               // battle_env.py:92
     s.ebx = g.team == 0 ? bbx : rbx; s.eby = g.team == 0 ? bby : rby;
     s.bhp_own = s.bhp_enemy = 5 * N;                                                // battle_env.py:91
-    if (rg) {
-#pragma unroll
-        for (int q = 0; q < SLOTS; ++q) rg->pos[q][threadIdx.x] = 0;
-    }
-    s.tick = 0; s.head = 0; s.env_done = 0; s.winner = W_NONE;
+    s.tick = 0; s.env_done = 0; s.winner = W_NONE;   // (the caller drops the env's bullets: kill / pool_filter)
 }
 
 // ---- state <-> registers / shared ring --------------------------------------------------------
 template <int N>
-__device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane<N> &s, Ring *rg, double &ret0,
-                                          double &ret1) {
+__device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane<N> &s, double &ret0, double &ret1) {
     constexpr int P = 2 * N;
-    const int tid = threadIdx.x;
     s.x = s.y = 0; s.hp = 0; s.dir = 0; s.ebx = s.eby = 64; s.bhp_own = s.bhp_enemy = 0;
-    s.tick = 0; s.head = 0; s.env_done = 1; s.winner = 0; s.episode = 0; ret0 = ret1 = 0;
+    s.tick = 0; s.env_done = 1; s.winner = 0; s.episode = 0; ret0 = ret1 = 0;
     if (g.valid) {
-        const long long a = g.e * P + g.i, EP = p.E * P;
-        if (rg) {
-#pragma unroll
-            for (int q = 0; q < SLOTS; ++q) {
-                rg->pos[q][tid] = p.bul_pos[q * EP + a];
-                rg->dlt[q][tid] = p.bul_dlt[q * EP + a];
-            }
-        }
+        const long long a = g.e * P + g.i;
         uint32_t pos = p.plane_pos[a];
         s.x = pos & 0xffff; s.y = pos >> 16;
         s.dir = p.plane_dir[a];
@@ -817,38 +749,27 @@ __device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane
         s.bhp_own = p.base_hp[g.e * 2 + g.team];
         s.bhp_enemy = p.base_hp[g.e * 2 + (1 - g.team)];
         uint32_t m = p.meta[g.e];
-        s.tick = m & 0xfff; s.head = (m >> 12) & 0xf; s.env_done = (m >> 16) & 0xff; s.winner = (m >> 24) & 0xff;
+        s.tick = m & 0xfff; s.env_done = (m >> 16) & 0xff; s.winner = (m >> 24) & 0xff;
         s.episode = p.episode[g.e];
         if (g.i == 0) { ret0 = p.ret[g.e * 2]; ret1 = p.ret[g.e * 2 + 1]; }
-    } else if (rg) {
-#pragma unroll
-        for (int q = 0; q < SLOTS; ++q) { rg->pos[q][tid] = 0; rg->dlt[q][tid] = 0; }
     }
 }
 
 template <int N>
-__device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, const Lane<N> &s, const Ring *rg,
-                                           double ret0, double ret1, bool base_pos_too) {
+__device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, const Lane<N> &s, double ret0, double ret1,
+                                           bool base_pos_too) {
     constexpr int P = 2 * N;
     if (!g.valid) return;
-    const int tid = threadIdx.x;
-    const long long a = g.e * P + g.i, EP = p.E * P;
+    const long long a = g.e * P + g.i;
     p.plane_pos[a] = (uint32_t)s.x | ((uint32_t)s.y << 16);
     p.plane_dir[a] = s.dir;
     p.plane_hp[a] = (int8_t)s.hp;
-    if (rg) {
-#pragma unroll
-        for (int q = 0; q < SLOTS; ++q) {
-            p.bul_pos[q * EP + a] = rg->pos[q][tid];
-            p.bul_dlt[q * EP + a] = rg->dlt[q][tid];
-        }
-    }
     if (g.k == 0) {  // first lane of each team owns its enemy's base record
         p.base_hp[g.e * 2 + (1 - g.team)] = (int16_t)s.bhp_enemy;
         if (base_pos_too) p.base_pos[g.e * 2 + (1 - g.team)] = (uint32_t)s.ebx | ((uint32_t)s.eby << 16);
     }
     if (g.i == 0) {
-        p.meta[g.e] = (uint32_t)s.tick | ((uint32_t)s.head << 12) | ((uint32_t)s.env_done << 16) | ((uint32_t)s.winner << 24);
+        p.meta[g.e] = (uint32_t)s.tick | ((uint32_t)s.env_done << 16) | ((uint32_t)s.winner << 24);
         p.episode[g.e] = s.episode;
         p.ret[g.e * 2] = ret0; p.ret[g.e * 2 + 1] = ret1;
     }
