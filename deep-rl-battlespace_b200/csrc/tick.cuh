@@ -594,9 +594,18 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
 // wvalid: the warp owns envs of this launch (the last block's spare warps, and in a chunked launch the
 // warps past the chunk, must neither read nor write a pool).
 __device__ __forceinline__ void pool_load(const Params &p, long long gw, bool wvalid, int lane, WarpPool &w, int &cnt) {
+    // The first POOL_SPEC entries are fetched without waiting for the count (the slots always exist), so
+    // that count, entries and the caller's other state loads share ONE memory round trip.
+    constexpr int POOL_SPEC = 4;  // x 32 entries: covers the typical 3v3 warp (~120 live bullets)
+    const uint2 *src = p.pool + (wvalid ? gw : 0) * POOL_CAP;
+    uint2 v[POOL_SPEC];
+#pragma unroll
+    for (int q = 0; q < POOL_SPEC; ++q) v[q] = src[q * 32 + lane];
     cnt = wvalid ? p.pool_cnt[gw] : 0;
-    const uint2 *src = p.pool + gw * POOL_CAP;
-    for (int idx = lane; idx < cnt; idx += 32) { const uint2 v = src[idx]; w.pos[idx] = v.x; w.meta[idx] = v.y; }
+#pragma unroll
+    for (int q = 0; q < POOL_SPEC; ++q)
+        if (q * 32 + lane < cnt) { w.pos[q * 32 + lane] = v[q].x; w.meta[q * 32 + lane] = v[q].y; }
+    for (int idx = POOL_SPEC * 32 + lane; idx < cnt; idx += 32) { const uint2 e = src[idx]; w.pos[idx] = e.x; w.meta[idx] = e.y; }
     w.ev[lane] = 0; w.cand[lane] = 0;
     __syncwarp();
 }
