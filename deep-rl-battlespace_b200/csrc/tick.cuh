@@ -508,7 +508,7 @@ struct WarpPool {
     uint32_t pos[POOL_CAP], meta[POOL_CAP];
     uint32_t ev[32], cand[32];   // per owner lane: event codes / candidate ages of this tick
     uint32_t candt[SLOTS][32];   // per (age index, owner): pool index << 8 | overlap mask
-    uint32_t plane[32];          // x | y << 16 | hp << 28 of every lane's plane (after the move)
+    uint32_t plane[32];          // x | y << 16 of every lane's plane after the move (0x7fff7fff: not alive)
     uint32_t baseT[32];          // enemy-base test word | first lane of the enemy team << 27
 };
 
@@ -528,7 +528,8 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
                                               bool kill, unsigned &ev, int &died_ai) {
     const int lane = g.lane;
     const unsigned lt = (1u << lane) - 1u;
-    w.plane[lane] = (uint32_t)s.x | ((uint32_t)s.y << 16) | ((uint32_t)(s.hp > 0 ? s.hp : 0) << 28);
+    // a plane that is not in self.agents is published far off the field: every rect test against it fails
+    w.plane[lane] = s.hp > 0 ? ((uint32_t)s.x | ((uint32_t)s.y << 16)) : 0x7fff7fffu;
     const unsigned runmask = __ballot_sync(FULL, c.run), killmask = __ballot_sync(FULL, kill);
     const unsigned sp = __ballot_sync(FULL, c.spawnP != 0);
     if (c.spawnP) {
@@ -549,7 +550,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         const int age = (int)(M >> 28) + 1;             // updates including this one
         const int ai = SLOTS - age;                     // age index, 0 = oldest
         const bool live = (P & B_VALID) != 0;
-        const bool killed = ((killmask >> owner) & 1u) && age >= 2;
+        const bool killed = killmask != 0 && ((killmask >> owner) & 1u) && age >= 2;  // (killmask: warp-uniform, rarely set)
         const bool moves = live && !killed && ((runmask >> owner) & 1u);
         bool keep = live && !killed;
         unsigned cm = 0;
@@ -563,8 +564,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
                 const int eb = bt >> 27;
 #pragma unroll
                 for (int j = 0; j < N; ++j) {
-                    const uint32_t e = w.plane[eb + j];
-                    cm |= ((e >> 28) != 0 && rect_hit(Pp - (e & 0x03ff07ffu), 55u, 50u) ? 1u : 0u) << j;
+                    cm |= (rect_hit(Pp - w.plane[eb + j], 55u, 50u) ? 1u : 0u) << j;
                 }
                 M += 1u << 28;
             }
