@@ -217,11 +217,18 @@ __device__ __forceinline__ float pair_angle(double t, double a0) {
 // needs enemy POSITIONS from a gather() after the move (hp may still change)
 template <int N>
 __device__ __forceinline__ void observe_issue(const Params &p, const Lane<N> &s, ObsLoads<N> &q) {
-    // every lane issues all its table loads (dead planes keep an on-field position); selects follow
-    pair_load(p, s.x - s.ebx, s.y - s.eby, q.t[0], q.od[0]);
+    // Only pairs that can still be observed are fetched: an observer or an enemy that is dead now stays
+    // dead (hp / am may only shrink before observe_finish, whose selects have the last word).  The gathers
+    // are this path's scarcest resource -- ~1/3 of them used to be issued for dead planes.
+    const bool me = s.hp > 0;
+    q.t[0] = 0; q.od[0] = 0;
+    if (me) pair_load(p, s.x - s.ebx, s.y - s.eby, q.t[0], q.od[0]);
 #pragma unroll
-    for (int j = 0; j < N; ++j)
-        pair_load(p, s.x - (int)(s.exy[j] & 0xffffu), s.y - (int)(s.exy[j] >> 16), q.t[j + 1], q.od[j + 1]);
+    for (int j = 0; j < N; ++j) {
+        q.t[j + 1] = 0; q.od[j + 1] = 0;
+        if (me && ((s.am >> j) & 1u))
+            pair_load(p, s.x - (int)(s.exy[j] & 0xffffu), s.y - (int)(s.exy[j] >> 16), q.t[j + 1], q.od[j + 1]);
+    }
 }
 
 // observe -- battle_env.py:202-244, for the lane's own plane; needs the final s.hp / s.am
