@@ -486,7 +486,7 @@ static int fail(int code, const std::string &msg) { g_err = msg; return code; }
             return fail(BS_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));            \
     } while (0)
 
-struct ObsTables { double *t360 = nullptr; float *odt = nullptr; size_t bytes = 0; bool persist = false; };
+struct ObsTables { double2 *tab = nullptr; size_t bytes = 0; bool persist = false; };
 
 struct bs_handle {
     bs_config cfg;
@@ -523,33 +523,31 @@ static int obs_tables_for(int device, ObsTables *out) {
     std::lock_guard<std::mutex> lk(g_tables_mu);
     if (device < 0 || device >= 64) return fail(BS_E_INVALID, "device index out of range");
     ObsTables &tb = g_tables[device];
-    if (!tb.t360) {
-        std::vector<double> t((size_t)T_W * T_H);
-        std::vector<float> od((size_t)OD_W * OD_H);
-        const double two_pi = 2 * M_PI;                                   // 2*math.pi
+    if (!tb.tab) {
+        // record (dx, dy >= 0): atan2(dy, dx) and float32(dist/diag*2-1).  atan2(-dy, dx) is recovered on the
+        // device as -atan2(dy, dx): checked here, bit for bit, against this machine's libm for every offset.
+        std::vector<double2> rec((size_t)T_W * T_H);
         const volatile double diag = std::sqrt(std::pow(1200.0, 2) + std::pow(800.0, 2));  // battle_env.py:230
-        for (int dy = -T_DY; dy <= T_DY; ++dy)
-            for (int dx = -T_DX; dx <= T_DX; ++dx) {
-                volatile double r = std::atan2((double)dy, (double)dx);  // battle_env.py:46
-                if (r < 0) r = r + two_pi;                                // rads %= 2*math.pi (float_rem)
-                volatile double degs = r * (180.0 / M_PI);               // math.degrees
-                t[(size_t)(dy + T_DY) * T_W + (dx + T_DX)] = 360 - degs;  // battle_env.py:49
-            }
         for (int dy = 0; dy <= T_DY; ++dy)
-            for (int dx = 0; dx <= T_DX; ++dx) {
-                volatile double d = std::sqrt((double)(dx * dx + dy * dy));  // battle_env.py:58
+            for (int dx = -T_DX; dx <= T_DX; ++dx) {
+                volatile double r = std::atan2((double)dy, (double)dx);      // battle_env.py:46
+                if (dy > 0) {
+                    volatile double rn = std::atan2((double)-dy, (double)dx);
+                    if (rn != -r) return fail(BS_E_UNSUPPORTED, "host libm atan2 is not odd in y: observation table cannot be folded");
+                }
+                volatile double d = std::sqrt((double)(dx * dx + dy * dy)); // battle_env.py:58
                 volatile double a = d / diag;
                 volatile double b = a * 2;
-                od[(size_t)dy * OD_W + dx] = (float)(b - 1);                  // stored into a float32 array, :230
+                const float od = (float)(b - 1);                            // stored into a float32 array, :230
+                uint32_t bits; std::memcpy(&bits, &od, 4);
+                double packed; const uint64_t w64 = bits; std::memcpy(&packed, &w64, 8);
+                rec[(size_t)dy * T_W + (dx + T_DX)] = make_double2(r, packed);
             }
-        // one allocation, so that a single access-policy window covers both tables
-        const size_t tbytes = t.size() * sizeof(double), obytes = od.size() * sizeof(float);
-        char *blk = nullptr;
-        CU(cudaMalloc(&blk, tbytes + obytes));
-        double *dt = (double *)blk; float *dd = (float *)(blk + tbytes);
-        CU(cudaMemcpy(dt, t.data(), tbytes, cudaMemcpyHostToDevice));
-        CU(cudaMemcpy(dd, od.data(), obytes, cudaMemcpyHostToDevice));
-        tb.bytes = tbytes + obytes;
+        const size_t tbytes = rec.size() * sizeof(double2);
+        double2 *blk = nullptr;
+        CU(cudaMalloc(&blk, tbytes));
+        CU(cudaMemcpy(blk, rec.data(), tbytes, cudaMemcpyHostToDevice));
+        tb.bytes = tbytes;
         // Pin the tables in L2: set aside enough persisting L2 for them (B200: 126 MB L2).
         cudaDeviceProp prop;
         CU(cudaGetDeviceProperties(&prop, device));
@@ -558,7 +556,7 @@ static int obs_tables_for(int device, ObsTables *out) {
             cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, tb.bytes + (4u << 20)) == cudaSuccess)
             tb.persist = true;
         cudaGetLastError();
-        tb.t360 = dt; tb.odt = dd;
+        tb.tab = blk;
     }
     *out = tb;
     return BS_OK;
@@ -600,7 +598,7 @@ static cudaError_t launch(const bs_handle *h, void (*kern)(KArgs...), int grid, 
     cudaLaunchAttribute attr[1];
     if (h->tables.persist) {
         attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
-        attr[0].val.accessPolicyWindow.base_ptr = (void *)h->tables.t360;
+        attr[0].val.accessPolicyWindow.base_ptr = (void *)h->tables.tab;
         attr[0].val.accessPolicyWindow.num_bytes = h->tables.bytes;
         attr[0].val.accessPolicyWindow.hitRatio = 1.0f;
         attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
@@ -702,7 +700,7 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     }
     ObsTables tb;
     if ((rc = obs_tables_for(device, &tb))) { bs_destroy(h); return rc; }
-    p.t360 = tb.t360; p.odt = tb.odt; h->tables = tb;
+    p.obs_tab = tb.tab; h->tables = tb;
     p.ep_log = nullptr; p.ep_cap = 0;
     // every env starts "done" (nothing spawned yet): the first reset / rollout tick spawns it
     std::vector<uint32_t> meta((size_t)n_envs, 1u << 16);

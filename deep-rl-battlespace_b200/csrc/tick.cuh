@@ -57,10 +57,11 @@ struct Params {
     uint32_t *episode;    // [E]
     double *ret;          // [E*2]
     unsigned long long *counters;  // [8] report counters + [1] episode-log cursor
-    // Observation tables, built once per device by the host with the host libm -- the libm CPython's
-    // math module calls -- and kept resident in the 126 MB L2 (DESIGN.md "Observation tables").
-    const double *t360;   // [T_H][T_W]   360 - degrees(atan2(dy,dx) mod 2pi), battle_env.py:46-49
-    const float *odt;     // [OD_H][OD_W] float32(sqrt(dx^2+dy^2)/diag*2-1),   battle_env.py:54-58,230
+    // Observation table, built once per device by the host with the host libm -- the libm CPython's
+    // math module calls -- and kept resident in the 126 MB L2 (DESIGN.md "Observation table"): one
+    // 16-byte record per integer offset (dx, |dy|), fetched with ONE 128-bit gather per observed pair.
+    const double2 *obs_tab;  // [T_DY+1][T_W]: .x = atan2(|dy|, dx) (battle_env.py:46), low word of .y =
+                             // float32(sqrt(dx^2+dy^2)/diag*2-1) (battle_env.py:54-58,230)
     // Optional per-episode score log (main.py:219-221 score_dict): ring of {red score, blue score, code};
     // code = 1 red won, 2 blue won, 3 tie, 6 both bases fell in the same tick.  counters[8] is its cursor.
     float *ep_log;        // [ep_cap][3] or nullptr
@@ -68,8 +69,7 @@ struct Params {
 };
 
 // Table geometry: every pair of on-field points (sprites.py:9-10) has dx in [-1200,1200], dy in [-800,800].
-constexpr int T_DX = 1200, T_DY = 800, T_W = 2 * T_DX + 1, T_H = 2 * T_DY + 1;
-constexpr int OD_W = T_DX + 1, OD_H = T_DY + 1;
+constexpr int T_DX = 1200, T_DY = 800, T_W = 2 * T_DX + 1, T_H = T_DY + 1;
 
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al. 2011); counter layout in include/battlespace.h
@@ -198,16 +198,25 @@ __device__ __forceinline__ float div360_f32(double rel) {
 // the gathers hides behind tick_end instead of stalling the warp.
 template <int N>
 struct ObsLoads {
-    double t[N + 1];
+    double r[N + 1];   // atan2(|dy|, dx) of the pair
     float od[N + 1];
+    unsigned neg;      // bit k: dy < 0 for pair k, i.e. atan2(dy, dx) = -r[k] (atan2 is odd in y; the host
+                       // verifies that its libm honours this bit for bit when it builds the table)
 };
 
-__device__ __forceinline__ void pair_load(const Params &p, int dx, int dy, double &t, float &od) {
-    od = __ldg(p.odt + abs(dy) * OD_W + abs(dx));
-    t = __ldg(p.t360 + (dy + T_DY) * T_W + (dx + T_DX));
+__device__ __forceinline__ void pair_load(const Params &p, int dx, int dy, double &r, float &od) {
+    const double2 rec = __ldg(p.obs_tab + abs(dy) * T_W + (dx + T_DX));
+    r = rec.x;
+    od = __int_as_float(__double2loint(rec.y));
 }
 
-__device__ __forceinline__ float pair_angle(double t, double a0) {
+// rel_angle -- battle_env.py:38-52 from r = atan2(|dy|, dx): the reference's own operations in its own
+// order, one rounding each: rads %= 2*pi (for a negative angle: + 2*pi), degrees(), 360 - degs, then
+// 180 + direction - that, wrapped into (-180, 180].
+__device__ __forceinline__ float pair_angle(double r0, bool neg, double a0) {
+    double r = neg ? -r0 : r0;
+    if (r < 0) r += TWO_PI;
+    const double t = 360 - r * RAD2DEG;
     double rel = 180 + a0 - t;
     if (rel < -180) rel += 360;
     if (rel > 180) rel -= 360;
@@ -221,13 +230,15 @@ __device__ __forceinline__ void observe_issue(const Params &p, const Lane<N> &s,
     // dead (hp / am may only shrink before observe_finish, whose selects have the last word).  The gathers
     // are this path's scarcest resource -- ~1/3 of them used to be issued for dead planes.
     const bool me = s.hp > 0;
-    q.t[0] = 0; q.od[0] = 0;
-    if (me) pair_load(p, s.x - s.ebx, s.y - s.eby, q.t[0], q.od[0]);
+    q.r[0] = 0; q.od[0] = 0;
+    q.neg = s.y - s.eby < 0 ? 1u : 0u;
+    if (me) pair_load(p, s.x - s.ebx, s.y - s.eby, q.r[0], q.od[0]);
 #pragma unroll
     for (int j = 0; j < N; ++j) {
-        q.t[j + 1] = 0; q.od[j + 1] = 0;
-        if (me && ((s.am >> j) & 1u))
-            pair_load(p, s.x - (int)(s.exy[j] & 0xffffu), s.y - (int)(s.exy[j] >> 16), q.t[j + 1], q.od[j + 1]);
+        q.r[j + 1] = 0; q.od[j + 1] = 0;
+        const int dy = s.y - (int)(s.exy[j] >> 16);
+        q.neg |= (dy < 0 ? 1u : 0u) << (j + 1);
+        if (me && ((s.am >> j) & 1u)) pair_load(p, s.x - (int)(s.exy[j] & 0xffffu), dy, q.r[j + 1], q.od[j + 1]);
     }
 }
 
@@ -235,12 +246,12 @@ __device__ __forceinline__ void observe_issue(const Params &p, const Lane<N> &s,
 template <int N>
 __device__ __forceinline__ void observe_finish(const Lane<N> &s, const ObsLoads<N> &q, float (&o)[3 * N + 2]) {
     const bool me = s.hp > 0;
-    o[0] = me ? q.od[0] : -1.0f; o[1] = me ? pair_angle(q.t[0], s.dir) : -1.0f;
+    o[0] = me ? q.od[0] : -1.0f; o[1] = me ? pair_angle(q.r[0], q.neg & 1u, s.dir) : -1.0f;
 #pragma unroll
     for (int j = 0; j < N; ++j) {
         const bool seen = me && ((s.am >> j) & 1u);
         o[2 + 3 * j] = seen ? 1.0f : -1.0f; o[3 + 3 * j] = seen ? q.od[j + 1] : -1.0f;
-        o[4 + 3 * j] = seen ? pair_angle(q.t[j + 1], s.dir) : -1.0f;
+        o[4 + 3 * j] = seen ? pair_angle(q.r[j + 1], (q.neg >> (j + 1)) & 1u, s.dir) : -1.0f;
     }
 }
 
