@@ -682,6 +682,7 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     p.E = n_envs; p.env_offset = env_offset;
     p.seed_lo = (uint32_t)seed; p.seed_hi = (uint32_t)(seed >> 32);
     p.tie_tick = tie_tick_for(h->N);
+    { const char *ex = getenv("BS_EXACT_TRIG"); p.exact_trig = ex && ex[0] == '1'; }
     p.r_hit_base = cfg->hit_base_reward; p.r_hit_plane = cfg->hit_plane_reward;
     p.r_miss = cfg->miss_punishment; p.r_die = cfg->die_punishment; p.r_lose = cfg->lose_punishment;
     p.diag = std::sqrt(std::pow(1200.0, 2) + std::pow(800.0, 2));

@@ -43,6 +43,7 @@ struct Params {
     long long env_offset; // global index of env 0 (sharding)
     uint32_t seed_lo, seed_hi;
     int tie_tick;         // first step call whose accumulated 0.1s reach 10+2N (battle_env.py:316-319)
+    int exact_trig;       // BS_EXACT_TRIG=1 at bs_create: never speculate in fp32 (cos_sin_fast); for the parity test
     double r_hit_base, r_hit_plane, r_miss, r_die, r_lose;
     double diag;          // == DIAG
     // SoA state (see DESIGN.md "Data layout in HBM")
@@ -331,11 +332,11 @@ __device__ __forceinline__ bool floor_guarded(float v, int &fl) {
 // integers all the time): x + st*cos >= 25 - 27.5, and any negative sum clamps to 25 whether it is
 // truncated or floored, so trunc(x + v) == x + floor(v) for the purpose of the clamped result.
 template <bool FAST>
-__device__ __forceinline__ void plane_forward(int &x, int &y, double dir, double speed) {
+__device__ __forceinline__ void plane_forward(int &x, int &y, double dir, double speed, bool exact) {
     const double st = speed * 0.1;
     int nx, ny;
     bool done = false;
-    if (FAST) {
+    if (FAST && !exact) {
         float cs, sn;
         cos_sin_fast(dir, cs, sn);
         const float stf = (float)st;
@@ -431,7 +432,7 @@ __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lan
             if (adisc == 2) mdir = plane_rotate(s.dir, 15);
             if (adisc == 3) mdir = plane_rotate(s.dir, -15);
         }
-        if (move) plane_forward<CONT>(s.x, s.y, mdir, speed);
+        if (move) plane_forward<CONT>(s.x, s.y, mdir, speed, p.exact_trig != 0);
         if (CONT) { s.dir = plane_rotate(s.dir, a[1] * 35); shoot = a[2] > 0; }
         else s.dir = mdir;
     }
@@ -443,7 +444,7 @@ __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lan
         const double bdir = d0 + (spread_u * 8 - 4);
         const uint32_t at = (((uint32_t)x0 | ((uint32_t)y0 << 16)) + B_BIAS) | B_VALID;
         bool done = false;
-        if (CONT) {  // fp32 speculation, see cos_sin_fast: a guarded floor is never an exact integer
+        if (CONT && !p.exact_trig) {  // fp32 speculation, see cos_sin_fast: a guarded floor is never an exact integer
             float cs, sn;
             cos_sin_fast(bdir, cs, sn);
             int fx, fy;

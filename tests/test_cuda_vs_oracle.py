@@ -275,3 +275,23 @@ def test_step_team_replay_equals_fused_rollout(N, cont, E, ticks, auto, cuda_dev
     for x, y in ((ra.state_mem, rb.state_mem), (ra.new_state_mem, rb.new_state_mem), (ra.action_mem, rb.action_mem),
                  (ra.rew_mem, rb.rew_mem), (ra.done_mem, rb.done_mem)):
         assert torch.equal(x, y)
+
+
+def test_fp32_speculated_trig_never_changes_the_result(cuda_device, monkeypatch):
+    """The fp32 speculation of the plane-move / bullet-step cosine (tick.cuh cos_sin_fast, guard 2.5e-4
+    against an error bound of 3.2e-5) must give the state of the exact double path, bit for bit:
+    65,536 envs x 320 ticks = 1.3e8 plane-ticks, both policies shooting as often as possible."""
+    from battlespace import parallel_env
+    kw = dict(n_agents=3, continuous_actions=True, n_envs=65536, seed=21, hit_base_reward=1.0, hit_plane_reward=0.9,
+              miss_punishment=-0.02, die_punishment=-0.03, lose_punishment=-0.05)
+    fast = parallel_env(**kw)
+    monkeypatch.setenv("BS_EXACT_TRIG", "1")
+    exact = parallel_env(**kw)
+    monkeypatch.delenv("BS_EXACT_TRIG")
+    for _ in range(10):
+        fast.rollout(32, "random", "instinct_ff")
+        exact.rollout(32, "random", "instinct_ff")
+    assert np.array_equal(fast.stats(), exact.stats()) and fast.stats()[3] > 100000
+    a, b = fast.get_state(), exact.get_state()
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
