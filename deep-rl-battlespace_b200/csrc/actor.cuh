@@ -53,7 +53,7 @@ struct ActorArgs {
 }  // namespace bs
 
 // launches actor_kernel<3N+2, cont ? 3 : 4> (defined in actor.cu)
-cudaError_t bs_launch_actor_impl(int n_agents, bool cont, const bs::ActorArgs &aa, cudaStream_t st);
+cudaError_t bs_launch_actor_impl(int n_agents, bool cont, const bs::ActorArgs &aa, cudaStream_t st, bool pdl = false);
 
 #ifdef BS_ACTOR_KERNELS
 namespace bs {
@@ -181,6 +181,10 @@ __global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
 #pragma unroll
         for (int c = 0; c < L; ++c) onext[c] = ok ? __ldg(src + c) : 0.0f;
     };
+    // programmatic dependent launch (bs_rollout_actor): the parameters above were staged while the
+    // previous grid (the env step that writes the observations) was still draining
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;");
     fetch(blockIdx.x);
     for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const long long e = tile * TM + tid;

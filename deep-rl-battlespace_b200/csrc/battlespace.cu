@@ -142,6 +142,10 @@ __global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, 
     Geo<N> g(gw, p.E);
     Lane<N> s;
     double ret0, ret1;
+    // programmatic dependent launch (bs_rollout_actor): nothing is read before the previous grid has
+    // completed; the next grid may be scheduled as soon as every block of this one has started
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;");
     load_lane(p, g, s, ret0, ret1);
     int cnt;
     pool_load(p, gw, gw < p.W, g.lane, w, cnt);
@@ -589,21 +593,29 @@ static int tie_tick_for(int n_agents) {  // battle_env.py:316-319: total_time ac
     for (;;) { ++k; t = t + 0.1; if (t >= 10 + 2 * n_agents) return k; }
 }
 
+static thread_local bool g_pdl = false;  // set by bs_rollout_actor around its launch loop
+
 // Kernel launch with the observation tables marked persisting in L2 for this launch only (the
 // caller's stream is not modified).
 template <class... KArgs, class... Args>
 static cudaError_t launch(const bs_handle *h, void (*kern)(KArgs...), int grid, int block, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
+    if (g_pdl) {  // programmatic dependent launch: this kernel may start while its predecessor drains (bs_rollout_actor)
+        attr[cfg.numAttrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[cfg.numAttrs].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs += 1;
+    }
     if (h->tables.persist) {
-        attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
-        attr[0].val.accessPolicyWindow.base_ptr = (void *)h->tables.tab;
-        attr[0].val.accessPolicyWindow.num_bytes = h->tables.bytes;
-        attr[0].val.accessPolicyWindow.hitRatio = 1.0f;
-        attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-        cfg.attrs = attr; cfg.numAttrs = 1;
+        cudaLaunchAttribute &a = attr[cfg.numAttrs];
+        a.id = cudaLaunchAttributeAccessPolicyWindow;
+        a.val.accessPolicyWindow.base_ptr = (void *)h->tables.tab;
+        a.val.accessPolicyWindow.num_bytes = h->tables.bytes;
+        a.val.accessPolicyWindow.hitRatio = 1.0f;
+        a.val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        a.val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        cfg.attrs = attr; cfg.numAttrs += 1;
     }
     return cudaLaunchKernelEx(&cfg, kern, args...);
 }
@@ -629,7 +641,7 @@ static inline int grid_for_envs(int64_t E, int N, int block = BLOCK) {
 
 // ---- actors (row f1) -------------------------------------------------------------------------------
 static int launch_actor(bs_handle *h, const ActorArgs &aa, cudaStream_t st) {
-    CU(bs_launch_actor_impl(h->N, h->cont, aa, st));
+    CU(bs_launch_actor_impl(h->N, h->cont, aa, st, g_pdl));
     return BS_OK;
 }
 
@@ -861,6 +873,10 @@ int bs_rollout_actor(bs_handle *h, int T, int learner_team, const bs_actor *acto
     sa.obs_in = obs;  // the buffer holds every env's current observation: no need to rebuild it before the tick
     sa.pol[1 - learner_team] = other_policy;
     if (replay && replay->capacity > 0) sa.rp = *replay;
+    // The two kernels of a tick are launched as programmatic dependents of each other: the actor kernel
+    // stages its parameters while the step kernel drains, and each grid is scheduled as the other's blocks
+    // exit instead of after a full launch gap (griddepcontrol.wait guards every dependent access).
+    struct PdlScope { PdlScope() { g_pdl = getenv("BS_NO_PDL") == nullptr; } ~PdlScope() { g_pdl = false; } } pdl_scope;
     for (int t = 0; t < T; ++t) {
         if ((rc = launch_actor(h, aa, st))) return rc;
         if (sa.rp.capacity > 0) sa.cursor_mod = (cursor + (int64_t)t * h->E) % sa.rp.capacity;
