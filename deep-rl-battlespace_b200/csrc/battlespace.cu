@@ -1188,7 +1188,7 @@ int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red,
         void *d_ext = nullptr;
         rc = stage_buf(h, 8, (size_t)T * pitch, &d_ext); if (rc) return rc;
         const int K = 32 / h->P;
-        int chunks = h->host_chunks > 0 ? h->host_chunks : 3;   // measured best of 1..15 at 65,536 envs (profiles/r1_e2e_chunks.txt)
+        int chunks = h->host_chunks > 0 ? h->host_chunks : 4;   // measured best of 3,4,6,8,12 at 65,536 envs (profiles/r1m_e2e_chunks.txt)
         int64_t per = (h->E + chunks - 1) / chunks;
         per = (per + K - 1) / K * K;                       // whole warps per chunk
         if (per < 4096) per = h->E;                        // small handles: one chunk
