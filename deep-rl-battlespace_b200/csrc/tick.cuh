@@ -263,6 +263,16 @@ __device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float
     observe_finish<N>(s, q, o);
 }
 
+// a / b for a compile-time divisor, correctly rounded, in 3 FMA-class instructions instead of the generic
+// division routine: with y = RN(1/b) and q = RN(a*y) (within 1 ulp of a/b), r = a - q*b is exact in an
+// FMA and RN(q + r*y) is the correctly rounded quotient (Markstein 1990).  |a| is at most a few thousand
+// here, far from over/underflow.
+__device__ __forceinline__ double div_const(double a, double b, double rcp_b) {
+    const double q = a * rcp_b;
+    const double r = fma(-q, b, a);
+    return fma(r, rcp_b, q);
+}
+
 // InstinctAgent.choose_action -- instinct/agent.py:10-62 (float32 obs decoded in double:
 // numpy 1.23.1 promotion).  Continuous: a[0..2]; discrete: adisc.
 template <int N, bool CONT>
@@ -281,8 +291,8 @@ __device__ __forceinline__ void instinct(const float (&o)[3 * N + 2], double sho
     if (CONT) {
         double a2 = 0;
         if (td < 500.0 / 3 * 2 && fabs(ta) < 20) a2 = shoot_u < 0.6 ? 1.0 : -1.0;
-        double a0 = td / DIAG * 2 - 1;
-        double v = -ta / 35, a1;
+        double a0 = div_const(td, DIAG, 1.0 / DIAG) * 2 - 1;
+        double v = div_const(-ta, 35.0, 1.0 / 35.0), a1;
         if (ta > 0) a1 = v > -1 ? v : -1; else a1 = v < 1 ? v : 1;
         double t0 = a0 + (-0.15 + (0.15 - -0.15) * n0);
         double t1 = a1 + (-0.15 + (0.15 - -0.15) * n1);
