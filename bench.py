@@ -90,6 +90,34 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def gpu_numa_cpus(device_index):
+    """CPUs of the NUMA node the GPU's PCIe root hangs off (None if the box does not say).  The e2e leg
+    streams 75 MB of pinned host memory per step: from the far socket that copy runs at ~60 % speed."""
+    try:
+        bus = torch.cuda.get_device_properties(device_index).pci_bus_id  # not in every torch build
+    except Exception:
+        bus = None
+    try:
+        if bus is None:
+            import subprocess
+            out = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(device_index)],
+                                 capture_output=True, text=True, timeout=20).stdout.strip()
+            bus = out.splitlines()[0].strip()
+        dom, b, rest = bus.lower().split(":")
+        path = f"/sys/bus/pci/devices/{dom[-4:]}:{b}:{rest}"
+        node = int(open(path + "/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        return cpus or None
+    except Exception:
+        return None
+
+
 def cpu_port_rate(steps, warmup, envs, threads=None):
     """agent-steps/s of the CPU port (oracle/) on the same workload, all host threads."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -207,6 +235,11 @@ def main():
     e2e = None
     if not args.no_e2e:
         k_e2e = max(3, min(args.steps, 40))
+        # the caller's thread and its pinned buffer sit on the GPU's own NUMA node for this leg only
+        # (the CPU baseline below uses every core again)
+        affinity0, near = os.sched_getaffinity(0), gpu_numa_cpus(dev.index)
+        if near:
+            os.sched_setaffinity(0, near)
         host_act = torch.empty((T, E, N, A), dtype=torch.float32).uniform_(-1, 1).pin_memory()
         for _ in range(3):
             env.rollout_host(T, "external", "instinct", 0, host_act, replay)
@@ -221,7 +254,9 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e = {"value": k_e2e * T * E * 2 * N * world / float(tt.item()), "unit": UNIT,
                "h2d_bytes_per_step": T * E * N * A * 4, "d2h_bytes_per_step": 64, "steps": k_e2e,
-               "call": "bs_rollout_fused_host (red actions [T,E,3,3] f32 from pinned host memory, counters back)"}
+               "call": "bs_rollout_fused_host (red actions [T,E,3,3] f32 from pinned host memory, counters back)",
+               "host_numa_bound": bool(near)}
+        os.sched_setaffinity(0, affinity0)
 
     if rank == 0:
         peak, peak_src = measured_peak()
