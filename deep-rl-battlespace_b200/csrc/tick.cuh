@@ -180,19 +180,20 @@ __device__ __forceinline__ void gather(const Geo<N> &g, Lane<N> &s) {
     }
 }
 
-// float32(rel / 360) for battle_env.py:231,242 without the double division: q = rel * (1/360) is
-// within 2 ulp of the quotient, so float(q) can differ from float(rel / 360) only when q lies within
-// a few double ulps of a float rounding midpoint (low 29 mantissa bits == 0x10000000); only then is
-// the division itself evaluated.  The result is the reference's float in every case.
-// out of line: inlined, the compiler evaluates the division speculatively on every call
-static __device__ __noinline__ float div360_exact(double rel) { return (float)(rel / 360); }
-
-__device__ __forceinline__ float div360_f32(double rel) {
-    const double q = rel * (1.0 / 360.0);
-    const uint32_t low = (uint32_t)__double2loint(q) & 0x1fffffffu;
-    if (low - 0x0ffffffcu <= 8u) return div360_exact(rel);
-    return (float)q;
+// a / b for a compile-time divisor, correctly rounded, in 3 FMA-class instructions instead of the generic
+// division routine: with y = RN(1/b) and q = RN(a*y) (within 1 ulp of a/b), r = a - q*b is exact in an
+// FMA and RN(q + r*y) is the correctly rounded quotient (Markstein 1990).  |a| is at most a few thousand
+// here, far from over/underflow.
+__device__ __forceinline__ double div_const(double a, double b, double rcp_b) {
+    const double q = a * rcp_b;
+    const double r = fma(-q, b, a);
+    return fma(r, rcp_b, q);
 }
+
+// float32(rel / 360) -- battle_env.py:231,242: the double quotient exactly as the reference rounds it, then
+// the float32 store.  (Until r1n this was rel * (1/360) with a guard that fell back to a real division
+// when the product sat within 4 ulps of a float rounding midpoint.)
+__device__ __forceinline__ float div360_f32(double rel) { return (float)div_const(rel, 360.0, 1.0 / 360.0); }
 
 // rel_angle / 360 -- battle_env.py:38-52,231 ; dist / diag * 2 - 1 -- battle_env.py:54-58,230.
 // atan2, the % 2pi, degrees() and the sqrt were evaluated by the host for every integer (dx, dy);
@@ -264,16 +265,6 @@ __device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float
     ObsLoads<N> q;
     observe_issue<N>(p, s, q);
     observe_finish<N>(s, q, o);
-}
-
-// a / b for a compile-time divisor, correctly rounded, in 3 FMA-class instructions instead of the generic
-// division routine: with y = RN(1/b) and q = RN(a*y) (within 1 ulp of a/b), r = a - q*b is exact in an
-// FMA and RN(q + r*y) is the correctly rounded quotient (Markstein 1990).  |a| is at most a few thousand
-// here, far from over/underflow.
-__device__ __forceinline__ double div_const(double a, double b, double rcp_b) {
-    const double q = a * rcp_b;
-    const double r = fma(-q, b, a);
-    return fma(r, rcp_b, q);
 }
 
 // InstinctAgent.choose_action -- instinct/agent.py:10-62 (float32 obs decoded in double:
