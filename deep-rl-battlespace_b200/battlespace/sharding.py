@@ -28,6 +28,24 @@ def allreduce_stats(local, group=None):
     return t.numpy() if is_np else t
 
 
+def broadcast_actors(actors, src=0, group=None):
+    """Config 5: after the learner rank's update, every rank's ``TeamActors`` takes
+    rank ``src``'s parameters -- ONE broadcast of the ~5.3k floats per plane packed into a flat
+    buffer (NCCL over NVLink for CUDA tensors, gloo for CPU ones).  The device pointers the kernels
+    hold stay valid: the parameters are overwritten in place."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1):
+        return actors
+    flat = torch.cat([t.reshape(-1) for row in actors.tensors for t in row])
+    dist.broadcast(flat, src=src, group=group)
+    off = 0
+    for row in actors.tensors:
+        for t in row:
+            t.copy_(flat[off:off + t.numel()].view_as(t))
+            off += t.numel()
+    return actors
+
+
 def summarize(stats):
     """Report-interval numbers of main.py:231-253 from the 8 counters."""
     s = [int(x) for x in stats]

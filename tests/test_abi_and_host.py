@@ -113,6 +113,46 @@ def test_sharded_stats_allreduce_gloo_world2(tmp_path):
     assert "OK" in outs[0]
 
 
+BCAST_WORKER = r"""
+import os, sys
+import numpy as np, torch
+import torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from battlespace.actors import STATE_KEYS, TeamActors
+from battlespace.sharding import broadcast_actors
+dist.init_process_group("gloo", rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]))
+rank = dist.get_rank()
+L, H, A, N = 11, 64, 3, 3
+shapes = [(H, L), (H,), (H,), (H,), (H, H), (H,), (H,), (H,), (A, H), (A,)]
+def params(seed):
+    rng = np.random.RandomState(seed)
+    return [{k: rng.randn(*s).astype(np.float32) for k, s in zip(STATE_KEYS, shapes)} for _ in range(N)]
+mine = TeamActors(params(100 + rank), "cpu")                  # every rank starts with different weights
+ptrs = [t.data_ptr() for row in mine.tensors for t in row]
+broadcast_actors(mine, src=0)
+want = params(100)
+for row, w in zip(mine.tensors, want):
+    for t, k in zip(row, STATE_KEYS):
+        assert np.array_equal(t.numpy(), w[k]), k
+assert ptrs == [t.data_ptr() for row in mine.tensors for t in row]   # in place: bs_actor pointers stay valid
+print("OK")
+dist.destroy_process_group()
+"""
+
+
+def test_broadcast_actors_gloo_world2(tmp_path):
+    """Config 5's weight broadcast: rank 1 ends with rank 0's actor parameters, in place."""
+    script = tmp_path / "bcast.py"
+    script.write_text(BCAST_WORKER)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29533", WORLD_SIZE="2", OMP_NUM_THREADS="2")
+    procs = [subprocess.Popen([sys.executable, str(script), os.path.join(ROOT, "deep-rl-battlespace_b200")],
+                              env=dict(env, RANK=str(r)), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+             for r in range(2)]
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert all("OK" in o for o in outs)
+
+
 def test_oracle_fused_rollout_equals_unfused_loop():
     """The oracle's fused rollout (what the CUDA rollout kernel is checked against) is the same
     game loop as reset + instinct + step (main.py:148-205), row for row."""
