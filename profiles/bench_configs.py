@@ -5,6 +5,7 @@ Run on the GPU box:  python profiles/bench_configs.py > gpurun_out/configs.jsonl
 
   modeA   : 3v3 continuous, 65,536 envs, single-tick bs_step with both teams' actions from HBM (SURVEY 8d Mode A)
   cfg2    : 2v2 discrete, 4,096 envs, shipped completed_model actors (PyTorch) vs in-kernel instinct
+  cfg2n   : the same with the actors in CUDA and the loop native (bs_rollout_actor)
   cfg4    : 5v5 continuous, instinct_ff vs instinct_ff (full bullet pool), 1,048,576 envs / world, fused T=32
   cfg5    : 3v3 discrete, 32,768 envs per GPU: PyTorch actor forward + bs_step_team_replay + reset of done envs
 """
@@ -102,6 +103,22 @@ def cfg2():
             "reference_anchor": "README.md:30 ~80 % wins; scores.json tail red 12.9 / blue 5.5 (with OU noise 0.4)"}
 
 
+def cfg2_native():
+    """cfg2 with the shipped completed_model actors evaluated by the CUDA actor kernel and the whole loop
+    native (bs_rollout_actor, no OU noise): the win-rate anchor through the product's own actor path."""
+    from battlespace import TeamActors
+    w = np.load(os.path.join(ROOT, "tests", "golden", "completed_model_actors.npz"))
+    E, N, T = 4096, 2, 32
+    actors = TeamActors.from_npz(w, [f"plane{k}" for k in range(N)], dev)
+    env = parallel_env(n_agents=N, n_envs=E, seed=0, device=dev, **CF)
+    env.reset_batched()
+    ms = timed(lambda: env.rollout_actor(T, actors, 0, "instinct"), 20, warm=2) / T
+    s = summarize(env.stats())
+    return {"case": "cfg2 native: 2v2 discrete, completed_model actors in CUDA (bs_rollout_actor) vs in-kernel instinct, 4096 envs",
+            "ms_per_tick": ms, "agent_steps_per_s": E * 2 * N / (ms * 1e-3), "games": s["games"],
+            "red_winrate": s["red_winrate"], "red_avg_score": s["red_avg_score"], "blue_avg_score": s["blue_avg_score"]}
+
+
 def cfg4():
     N, E, T = 5, 1 << 20, 32
     env = parallel_env(n_agents=N, continuous_actions=True, n_envs=E, seed=0, device=dev, **CF)
@@ -185,7 +202,7 @@ def cfg5_native():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["modeA", "cfg2", "cfg4", "cfg5", "cfg5n"]
-    fns = {"modeA": mode_a, "cfg2": cfg2, "cfg4": cfg4, "cfg5": cfg5, "cfg5n": cfg5_native}
+    which = sys.argv[1:] or ["modeA", "cfg2", "cfg2n", "cfg4", "cfg5", "cfg5n"]
+    fns = {"modeA": mode_a, "cfg2": cfg2, "cfg2n": cfg2_native, "cfg4": cfg4, "cfg5": cfg5, "cfg5n": cfg5_native}
     for name in which:
         print(json.dumps(fns[name]()), flush=True)
