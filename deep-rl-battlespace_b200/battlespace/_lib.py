@@ -60,7 +60,8 @@ class bs_ou_noise(C.Structure):
 
 
 class bs_sprites(C.Structure):
-    _fields_ = [("plane", C.c_void_p * 2), ("base", C.c_void_p * 2)]
+    _fields_ = [("plane", C.c_void_p * 2), ("base", C.c_void_p * 2), ("explosion_img", C.c_void_p),
+                ("explosions", C.c_void_p), ("n_explosions", C.c_int32)]
 
 
 STATE_FIELDS = ("plane_x", "plane_y", "plane_dir", "plane_hp", "base_pos", "base_hp", "bullet_pos",

@@ -93,6 +93,7 @@ class parallel_env:
         self.total_games = self.ties = 0
         self.bullet_speed, self.shot_dist, self.time_step = 450, 500, 0.1
         self.show, self.fps, self.recording = show, fps, False
+        self.explosions = []                    # battle_env.py:172: [x, y, frame] of the running animations
         self.hit_base_reward, self.hit_plane_reward = hit_base_reward, hit_plane_reward
         self.miss_punishment, self.die_punishment, self.lose_punishment = miss_punishment, die_punishment, lose_punishment
         self.winner, self.env_done = "none", True
@@ -213,8 +214,9 @@ class parallel_env:
     # rendering stays on the host and off the hot path (battle_env.py:426-447,498-580); this box has
     # no graphics stack, so these keep the call surface and do nothing.
     # ----- rendering (battle_env.py:498-581): headless CUDA frames, no window ---------
-    def render_frame(self, env=0, out=None, sprites=None):
-        """RGB uint8 [800,1200,3] device tensor of env ``env`` as ``render()`` would draw it."""
+    def render_frame(self, env=0, out=None, sprites=None, explosions=None):
+        """RGB uint8 [800,1200,3] device tensor of env ``env`` as ``render()`` would draw it.
+        ``explosions``: (x, y, frame) triples, the caller's ``self.explosions`` (battle_env.py:356,534-536)."""
         from .render import Sprites
         if sprites is not None:
             self._sprites = sprites
@@ -222,15 +224,30 @@ class parallel_env:
             self._sprites = Sprites(self.device, os.environ.get("BATTLESPACE_ASSETS"))
         if out is None:
             out = torch.empty((self.height, self.width, 3), dtype=torch.uint8, device=self.device)
-        check(lib.bs_render(self._h, int(env), C.byref(self._sprites.struct), _ptr(out), self._stream()))
+        check(lib.bs_render(self._h, int(env), C.byref(self._sprites.with_explosions(explosions)), _ptr(out), self._stream()))
         return out
+
+    def _track_explosions(self, env=0):
+        """self.explosions of the reference for env ``env``: a plane whose hp fell to 0 since the last
+        rendered frame of the same episode starts an animation at its centre (battle_env.py:351-356)."""
+        st = self.get_state()
+        hp, ep = st["plane_hp"][env].astype(np.int64), int(st["episode"][env])
+        prev = getattr(self, "_expl_prev", None)
+        if prev is not None and prev[0] == ep:
+            for i in np.nonzero((prev[1] > 0) & (hp <= 0))[0]:
+                self.explosions.append([int(st["plane_x"][env, i]), int(st["plane_y"][env, i]), 0])
+        self._expl_prev = (ep, hp)
 
     def render(self, mode="human"):
         """The reference opens a pygame window (unavailable here); this keeps its contract for the
         callers that matter: nothing unless ``show``; when recording, one frame of env 0 per call."""
         if not self.show:
             return None
-        frame = self.render_frame(0)
+        self._track_explosions(0)
+        frame = self.render_frame(0, explosions=self.explosions)
+        for ex in self.explosions:          # Explosion.draw advances its frame on every draw, sprites.py:405-419
+            ex[2] += 1
+        self.explosions = [ex for ex in self.explosions if ex[2] < 9]
         if self.recording and getattr(self, "video", None) is not None:
             self.video.update(frame.cpu().numpy())
         return frame

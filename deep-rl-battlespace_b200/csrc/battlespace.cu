@@ -912,7 +912,9 @@ int bs_render(bs_handle *h, int64_t env, const bs_sprites *sprites, uint8_t *rgb
     if (env < 0 || env >= h->E) return fail(BS_E_INVALID, "env index out of range");
     if (!sprites->plane[0] || !sprites->plane[1] || !sprites->base[0] || !sprites->base[1]) return fail(BS_E_INVALID, "null sprite");
     DeviceGuard guard(h->device);
-    RenderArgs ra{env, {sprites->plane[0], sprites->plane[1]}, {sprites->base[0], sprites->base[1]}, rgb};
+    if (sprites->n_explosions < 0) return fail(BS_E_INVALID, "n_explosions must be >= 0");
+    RenderArgs ra{env, {sprites->plane[0], sprites->plane[1]}, {sprites->base[0], sprites->base[1]}, rgb,
+                  sprites->explosion_img, sprites->explosions, sprites->n_explosions};
     const int grid = (R_W * R_H + 255) / 256;
     DISPATCH_N(h->N, render_kernel<N_><<<grid, 256, 0, (cudaStream_t)stream>>>(h->p, ra));
     CU(cudaGetLastError());

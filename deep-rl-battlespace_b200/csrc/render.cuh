@@ -3,8 +3,8 @@
 // (plane names, winner screen) and vidmaker are unavailable on this box and left out.
 //
 // Draw order of the reference: white background (:528), bullets (:531-532, 6x3 quads in the
-// shooter's colour rotated by their heading, sprites.py:306-311,353-360), explosions (:535-536,
-// omitted: the animation frames are host-side history, not env state), both bases with their
+// shooter's colour rotated by their heading, sprites.py:306-311,353-360), explosions (:535-536: the
+// caller's list of {x, y, frame}, the animation history is host-side like self.explosions), both bases with their
 // hp bar (:539-540, sprites.py:265-278), alive red then blue planes with their hp bar (:543-550,
 // sprites.py:155-178).  Sprites are RGBA images handed over by the caller (the reference's
 // assets/*.png or procedural stand-ins); a rotated sprite is sampled by inverse mapping with
@@ -21,12 +21,16 @@ namespace bs {
 constexpr int R_W = 1200, R_H = 800;                 // sprites.py:9-10
 constexpr int PLANE_W = 50, PLANE_H = 48, BASE_W = 62, BASE_H = 62, BUL_W = 6, BUL_H = 3;
 constexpr int Q = 14;                                // fixed-point bits of cos / sin
+constexpr int EXPL_W = 64, EXPL_FRAMES = 9, MAX_EXPL = 64;   // sprites.py:392-398
 
 struct RenderArgs {
     long long env;
     const uint8_t *plane_img[2];   // [48][50][4] RGBA, red / blue
     const uint8_t *base_img[2];    // [62][62][4]
     uint8_t *rgb;                  // [800][1200][3]
+    const uint8_t *expl_img;       // [9][64][64][4] or nullptr
+    const int32_t *expl;           // [n_expl][3] = x, y, frame
+    int n_expl;
 };
 
 struct RObj {            // one rotated rectangle: plane or bullet
@@ -69,7 +73,10 @@ __global__ void __launch_bounds__(256) render_kernel(Params p, RenderArgs ra) {
     __shared__ RObj obj[MAXO];
     __shared__ RBar bar[P + 2];
     __shared__ int base_xy[2][2];
+    __shared__ int expl[MAX_EXPL][3];
     const long long e = ra.env;
+    const int n_expl = ra.expl_img != nullptr && ra.expl != nullptr ? min(ra.n_expl, MAX_EXPL) : 0;
+    for (int q = threadIdx.x; q < n_expl * 3; q += blockDim.x) expl[q / 3][q % 3] = ra.expl[q];
     // ---- stage the env's objects: bullets first (drawn first), then planes -----------------------
     for (int q = threadIdx.x; q < P * SLOTS; q += blockDim.x) obj[q].kind = -1;
     __syncthreads();
@@ -144,6 +151,11 @@ __global__ void __launch_bounds__(256) render_kernel(Params p, RenderArgs ra) {
         }
     };
     for (int q = 0; q < P * SLOTS; ++q) rotated(obj[q]);
+    for (int q = 0; q < n_expl; ++q) {  // Explosion.draw, sprites.py:405-419: frame blitted at rect centred on the kill
+        const int f = expl[q][2], u = px_ - (expl[q][0] - EXPL_W / 2), v = py - (expl[q][1] - EXPL_W / 2);
+        if (f >= 0 && f < EXPL_FRAMES && u >= 0 && u < EXPL_W && v >= 0 && v < EXPL_W)
+            blend(out, ra.expl_img + ((size_t)(f * EXPL_W + v) * EXPL_W + u) * 4);
+    }
 #pragma unroll
     for (int t = 0; t < 2; ++t) {  // Base.draw, sprites.py:265-275: blit at rect (centre - 31), then the bar
         const int u = px_ - (base_xy[t][0] - BASE_W / 2), v = py - (base_xy[t][1] - BASE_H / 2);

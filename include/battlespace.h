@@ -226,13 +226,20 @@ int bs_replay_sample(const bs_replay *replay, int n_agents, int obs_len, int n_a
 typedef struct bs_sprites {
     const uint8_t *plane[2]; /* [48][50][4] */
     const uint8_t *base[2];  /* [62][62][4] */
+    /* Explosion animation (sprites.py:375-419): 9 frames scaled to 64 x 64, colour key black = alpha 0.
+     * NULL or n_explosions == 0: none drawn.  explosions = DEVICE int32 [n][3] {x, y, frame}: the caller
+     * keeps the list the reference keeps in self.explosions (one per killed plane, battle_env.py:356,
+     * frame + 1 per drawn frame, sprites.py:405-419); entries with frame outside 0..8 are skipped. */
+    const uint8_t *explosion_img;  /* [9][64][64][4] */
+    const int32_t *explosions;
+    int32_t n_explosions;          /* at most 64 are drawn */
 } bs_sprites;
 
 /* parallel_env.render (battle_env.py:498-560) for env `env` into rgb [800][1200][3] u8 (device), no
  * window: white background, bullets as 6x3 quads in the shooter's colour, both bases and the alive
  * planes (sprites rotated counter-clockwise by their direction about the rect centre, nearest
- * neighbour) with their hp bars.  Left out: explosion animation, plane names / winner text (fonts),
- * rounded bar corners.  Integer geometry (half-pixels, Q14 rotation): reproducible bit for bit. */
+ * neighbour) with their hp bars; explosions (between bullets and bases, battle_env.py:534-536) from the
+ * caller's list.  Left out: plane names / winner text (fonts), rounded bar corners.  Integer geometry (half-pixels, Q14 rotation): reproducible bit for bit. */
 int bs_render(bs_handle *h, int64_t env, const bs_sprites *sprites, uint8_t *rgb, void *stream);
 
 /* out[8] = {red wins, blue wins, ties, total_games, sum(red episode return)*2^20,

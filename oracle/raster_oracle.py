@@ -4,7 +4,8 @@ parallel_env.render (/root/reference/envs/battle_env.py:498-560; sprites.py:155-
 produces.  Parity status: **unpinned** against pygame itself -- pygame.transform.rotate and the display
 are unavailable on this box; what this pins is the documented geometry (half-pixel integer coordinates,
 Q14 rotation, nearest-neighbour inverse mapping, pygame's per-pixel-alpha blend formula), pixel for
-pixel.  Explosions, fonts (names, winner screen) and rounded bar corners are left out on both sides.
+pixel.  Explosions (Explosion.draw, sprites.py:405-419) are drawn from a caller-supplied list of
+(x, y, frame); fonts (names, winner screen) and rounded bar corners are left out on both sides.
 
 Input: the env state as returned by parallel_env.get_state() for ONE env, and the four RGBA sprites."""
 import numpy as np
@@ -50,8 +51,9 @@ def _bar(img, cx, cy, dy, hp, colour):
     img[clip(y0, H):clip(y0 + h, H), clip(x0, W):clip(x0 + w, W)] = colour
 
 
-def render(state, e, n_agents, plane_sprites, base_sprites):
-    """state: dict of numpy arrays from get_state(); returns uint8 [800,1200,3]."""
+def render(state, e, n_agents, plane_sprites, base_sprites, explosion_frames=None, explosions=()):
+    """state: dict of numpy arrays from get_state(); explosion_frames [9,64,64,4] RGBA and explosions =
+    (x, y, frame) triples drawn after the bullets (battle_env.py:534-536); returns uint8 [800,1200,3]."""
     N, P = n_agents, 2 * n_agents
     img = np.full((H, W, 3), 255, np.uint8)
     bp, bv = state["bullet_pos"][e], state["bullet_vel"][e]          # [2N,12,2], [2N,12,3]; slot = age-1
@@ -64,6 +66,13 @@ def render(state, e, n_agents, plane_sprites, base_sprites):
             c = int(np.rint(sx / ln * (1 << Q))) if ln > 0 else 1 << Q
             s = int(np.rint(-sy / ln * (1 << Q))) if ln > 0 else 0
             _rotated(img, int(bp[i, age, 0]), int(bp[i, age, 1]), c, s, 6, 3, colour=RED if i < N else BLUE)
+    for x, y, f in (explosions if explosion_frames is not None else ())[:64]:
+        if not 0 <= f < 9:
+            continue
+        x0, y0 = int(x) - 32, int(y) - 32                               # rect of the 64 x 64 frame centred on the kill
+        ys, xs = np.mgrid[max(y0, 0):min(y0 + 64, H), max(x0, 0):min(x0 + 64, W)]
+        if ys.size:
+            _blend(img, ys, xs, explosion_frames[f][ys - y0, xs - x0])
     for t in range(2):
         bx, by = int(state["base_pos"][e, t, 0]), int(state["base_pos"][e, t, 1])
         x0, y0 = bx - 31, by - 31

@@ -32,6 +32,48 @@ def test_frames_match_cpu_restatement(cuda_device, N, cont):
     assert bad == 0, bad
 
 
+def test_explosions_are_drawn_between_bullets_and_planes(cuda_device):
+    """Explosion.draw (sprites.py:405-419, battle_env.py:534-536): frames blitted from the caller's list, over
+    the bullets and under bases / planes; frames outside 0..8 and lists longer than 64 are cut."""
+    from battlespace import parallel_env
+    from battlespace.render import Sprites
+    import raster_oracle
+    N, E = 3, 8
+    env = parallel_env(n_agents=N, continuous_actions=True, n_envs=E, seed=4)
+    sp = Sprites(cuda_device)
+    env.rollout(40, "instinct_ff", "instinct")
+    st = env.get_state()
+    e = 5
+    px, py = int(st["plane_x"][e, 0]), int(st["plane_y"][e, 0])
+    bx, by = int(st["base_pos"][e, 1, 0]), int(st["base_pos"][e, 1, 1])
+    ex = [(px + 10, py - 5, 2), (bx - 20, by + 20, 8), (600, 400, 0), (5, 795, 4), (1199, 3, 7), (300, 300, 9), (300, 300, -1)]
+    got = env.render_frame(e, sprites=sp, explosions=ex).cpu().numpy()
+    want = raster_oracle.render(st, e, N, sp.host[0:2], sp.host[2:4], sp.host_explosion, ex)
+    plain = raster_oracle.render(st, e, N, sp.host[0:2], sp.host[2:4])
+    assert np.array_equal(got, want)
+    assert (want != plain).any(axis=-1).sum() > 500          # the animations are visible
+    assert np.array_equal(env.render_frame(e, sprites=sp).cpu().numpy(), plain)   # and the list does not stick
+    many = [(40 + 17 * k, 60 + 9 * k, k % 9) for k in range(80)]
+    assert np.array_equal(env.render_frame(e, sprites=sp, explosions=many).cpu().numpy(),
+                          raster_oracle.render(st, e, N, sp.host[0:2], sp.host[2:4], sp.host_explosion, many))
+
+
+def test_render_tracks_kills_as_explosions(cuda_device):
+    """render() keeps self.explosions like the reference: one animation per killed plane, 9 frames long."""
+    from battlespace import parallel_env
+    env = parallel_env(n_agents=2, show=True, n_envs=1, seed=3)
+    env.reset()
+    st = env.get_state()
+    env.render()                                             # first frame: remembers the hit points
+    st["plane_hp"][0, 1] = 0                                 # a plane dies between two frames
+    env.set_state(st)
+    env.render()
+    assert env.explosions == [[int(st["plane_x"][0, 1]), int(st["plane_y"][0, 1]), 1]]
+    for _ in range(8):
+        env.render()
+    assert env.explosions == []
+
+
 def test_recording_writes_a_video(cuda_device, tmp_path):
     """start_recording / export_video (battle_env.py:562-581) through the dict API with show=True."""
     cv2 = pytest.importorskip("cv2")
