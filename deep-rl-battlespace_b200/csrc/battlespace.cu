@@ -130,13 +130,18 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
     }
 }
 
+// 64-thread blocks, 12 resident (24 warps per SM at 80 registers): measured 1.5 % faster than 128 x 6 in Mode A
+// (finer-grained block turnover over the 3.7 waves); 7-8 blocks of 128 and 256-thread blocks are 4 % slower.
+#ifndef STEP_BLOCK
+#define STEP_BLOCK 64
+#endif
 #ifndef STEP_MIN_BLOCKS
-#define STEP_MIN_BLOCKS 6
+#define STEP_MIN_BLOCKS (768 / STEP_BLOCK)
 #endif
 template <int N, bool CONT>
-__global__ void __launch_bounds__(BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, StepArgs sa) {
+__global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, StepArgs sa) {
     constexpr int P = 2 * N, L = 3 * N + 2;
-    __shared__ WarpPool pools[BLOCK / 32];
+    __shared__ WarpPool pools[STEP_BLOCK / 32];
     WarpPool &w = pools[threadIdx.x >> 5];
     const long long gw = global_warp();
     Geo<N> g(gw, p.E);
@@ -750,9 +755,9 @@ int bs_reset(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float 
 }
 
 static int launch_step(bs_handle *h, const StepArgs &sa, cudaStream_t st) {
-    const int grid = grid_for_envs(h->E, h->N);
-    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true>, grid, BLOCK, st, h->p, sa))); }
-    else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false>, grid, BLOCK, st, h->p, sa))); }
+    const int grid = grid_for_envs(h->E, h->N, STEP_BLOCK);
+    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true>, grid, STEP_BLOCK, st, h->p, sa))); }
+    else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false>, grid, STEP_BLOCK, st, h->p, sa))); }
     return BS_OK;
 }
 
