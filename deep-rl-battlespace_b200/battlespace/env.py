@@ -65,7 +65,9 @@ class parallel_env:
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         if self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
-        self.seed = int(seed) if seed is not None else 0
+        # seed=None: a fresh seed per env object, like the reference's unseeded `random` module (independent runs
+        # must not replay the same spawn / spread stream); pass an int for reproducible runs
+        self.seed = int(seed) if seed is not None else int.from_bytes(os.urandom(8), "little") >> 1
         self.env_offset = int(env_offset)
 
         # --- attributes of the reference object, battle_env.py:86-184 --------------------------
@@ -127,6 +129,11 @@ class parallel_env:
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
+    def _host_call_barrier(self):
+        """The *_host entry points run on the handle's own streams: everything queued on the caller's torch
+        stream for this env (batched API calls, replay-ring fills) must have completed before they start."""
+        torch.cuda.current_stream(self.device).synchronize()
+
     def observation_space(self, agent):
         return self.observation_spaces[agent]
 
@@ -151,6 +158,7 @@ class parallel_env:
         self._need_single()
         obs = np.empty((1, self._P, self._L), np.float32)
         d = None if draws is None else np.ascontiguousarray(draws, np.int32).reshape(1, 4 + 6 * self.n_agents)
+        self._host_call_barrier()
         check(lib.bs_reset_host(self._h, None, _np_ptr(d), _np_ptr(obs)))
         self.winner, self.env_done = "none", False
         self.agents = self.possible_agents[:]
@@ -184,6 +192,7 @@ class parallel_env:
         obs = np.empty((1, P, L), np.float32); rew = np.empty((1, P), np.float32)
         done = np.empty((1, P), np.uint8); env_done = np.empty(1, np.uint8); winner = np.empty(1, np.int8)
         d = None if draws is None else np.ascontiguousarray(draws, np.float64).reshape(1, P, 5)
+        self._host_call_barrier()
         check(lib.bs_step_host(self._h, _np_ptr(arr), dtype, _np_ptr(d), _np_ptr(obs), _np_ptr(rew), _np_ptr(done),
                                _np_ptr(env_done), _np_ptr(winner)))
         was_done = self.env_done
@@ -211,8 +220,6 @@ class parallel_env:
     def make_discrete(self, actions_dict):
         return {a: np.argmax(v) for a, v in actions_dict.items()}
 
-    # rendering stays on the host and off the hot path (battle_env.py:426-447,498-580); this box has
-    # no graphics stack, so these keep the call surface and do nothing.
     # ----- rendering (battle_env.py:498-581): headless CUDA frames, no window ---------
     def render_frame(self, env=0, out=None, sprites=None, explosions=None):
         """RGB uint8 [800,1200,3] device tensor of env ``env`` as ``render()`` would draw it.
@@ -351,8 +358,31 @@ class parallel_env:
         check(lib.bs_instinct_actions(self._h, int(team), _ptr(obs), _ptr(draws), _ptr(out), self._stream()))
         return out
 
+    def _check_ext_actions(self, T, ext_actions, on_device):
+        """The learner's action block [T,E,N,A] float32 (BS_POL_EXTERNAL): the library reads it as a raw pointer."""
+        if ext_actions is None:
+            return
+        want = int(T) * self._E * self.n_agents * self.n_actions
+        if ext_actions.dtype != torch.float32 or ext_actions.numel() != want or not ext_actions.is_contiguous():
+            raise ValueError(f"ext_actions must be a contiguous float32 tensor [T,E,N,A] = {want} values, got "
+                             f"{tuple(ext_actions.shape)} {ext_actions.dtype}")
+        if on_device and ext_actions.device != self.device:
+            raise ValueError("ext_actions must live on the env's device")
+        if not on_device and ext_actions.device.type != "cpu":
+            raise ValueError("ext_actions_host must be a CPU (preferably pinned) tensor")
+
+    def _check_replay(self, replay, T):
+        """Ring rules of the C ABI (include/battlespace.h, bs_replay): rows of different envs never collide."""
+        if replay is None:
+            return
+        if replay.mem_size < self._E or (int(T) * self._E > replay.mem_size and replay.mem_size % self._E != 0):
+            raise ValueError(f"replay ring of {replay.mem_size} rows cannot take {T} x {self._E} rows per call: it needs "
+                             "capacity >= n_envs, and capacity % n_envs == 0 when one call wraps the ring")
+
     def rollout(self, T, red="random", blue="instinct", learner_team=0, ext_actions=None, replay=None, cursor=None):
         """T fused ticks with in-kernel policies, auto-reset and replay rows (main.py:178-213)."""
+        self._check_ext_actions(T, ext_actions, True)
+        self._check_replay(replay, T)
         rp = None
         if replay is not None:
             rp = replay.as_struct()
@@ -366,6 +396,9 @@ class parallel_env:
     def rollout_host(self, T, red="random", blue="instinct", learner_team=0, ext_actions_host=None, replay=None, cursor=None):
         """Same through the host-buffer entry point: ``ext_actions_host`` is a (pinned) CPU tensor
         [T,E,N,A]; returns the 8 counters as numpy int64 after the device work completed."""
+        self._check_ext_actions(T, ext_actions_host, False)
+        self._check_replay(replay, T)
+        self._host_call_barrier()
         rp = None
         if replay is not None:
             rp = replay.as_struct()

@@ -113,7 +113,8 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
             for (int c = 0; c < 3; ++c) { a[c] = 2 * u[1 + c] - 1; raw[c] = (float)a[c]; }
             adisc = 0;
         } else {
-            adisc = (int)(w[0] >> 30);
+            // Philox: the top two bits of w0; injected draws: the same two bits of noise_u0 = (w0 >> 8) / 2^24
+            adisc = draws_row != nullptr ? (int)(u[1] * 4.0) : (int)(w[0] >> 30);
 #pragma unroll
             for (int c = 0; c < 4; ++c) raw[c] = c == adisc ? 1.0f : 0.0f;
         }
@@ -172,7 +173,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     }
 
     // external actions
-    const int pol = sa.pol[g.team];
+    const int pol = g.team ? sa.pol[1] : sa.pol[0];  // (a dynamic index would make the compiler copy the parameter struct to local memory)
     const bool ext = g.valid && pol == POL_EXTERNAL && sa.dtype != ACT_NONE;
     int adisc = 0;
     double a[3] = {0, 0, 0}, spread_u = 0;
@@ -244,7 +245,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
         gather(g, s);  // enemy positions after the move, hp before the bullet loop
         if (want_obs) observe_issue<N>(p, s, q);
         unsigned ev; int died_ai;
-        bullets_dense<N>(g, s, w, cnt, c, false, ev, died_ai);
+        bullets_dense<N>(g, s, w, cnt, c, ev, died_ai);
         tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
         if (want_obs) observe_finish<N>(s, q, o);
     }
@@ -307,8 +308,7 @@ struct RolloutArgs {
     long long e0, e_end;  // env range of this launch (the host entry point pipelines chunks)
 };
 
-
-// warp-index arithmetic) and 32 resident blocks per SM give the same 32 warps as 8 blocks of 4.
+// 128-thread blocks x 8 resident (32 warps per SM at 64 registers); 6, 7, 9 and 10 resident blocks measured slower (r1).
 #ifndef ROLLOUT_BLOCK
 #define ROLLOUT_BLOCK 128
 #endif
@@ -331,7 +331,8 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
     float o[L];
     observe<N>(p, s, o);
     Tally tl;
-    const int pol = ra.pol[g.team];
+    const int pol = g.team ? ra.pol[1] : ra.pol[0];  // (a dynamic index would make the compiler copy the parameter struct to local memory:
+                                                      //  r1o spent 9 % of its stall samples on those reloads)
     const bool writer = g.valid && g.team == ra.learner && ra.rp.capacity > 0;
     long long row = 0;
     if (ra.rp.capacity > 0) row = (ra.cursor_mod + g.e % ra.rp.capacity) % ra.rp.capacity;
@@ -342,6 +343,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
         const bool need = g.valid && s.env_done;
         if (__any_sync(FULL, need)) {
             if (need) { reset_lane(p, g, s, false, nullptr); ret0 = ret1 = 0; pool_publish_base<N>(g, s, w); }
+            pool_filter(w, cnt, __ballot_sync(FULL, need), g.lane);  // the finished games' bullets vanish, battle_env.py:272
             gather(g, s);
             float o2[L];
             observe<N>(p, s, o2);
@@ -388,7 +390,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
             tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, false, c);
             unsigned ev; int died_ai;
             gather(g, s);  // enemy positions after the move, hp before the bullet loop
-            bullets_dense<N>(g, s, w, cnt, c, need, ev, died_ai);
+            bullets_dense<N>(g, s, w, cnt, c, ev, died_ai);
             ObsLoads<N> q;
             observe_issue<N>(p, s, q);  // positions are final; hp / alive masks are settled by then
             tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
@@ -698,6 +700,7 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     Params &p = h->p;
     p.E = n_envs; p.env_offset = env_offset;
     p.seed_lo = (uint32_t)seed; p.seed_hi = (uint32_t)(seed >> 32);
+    philox_round_keys(p.seed_lo, p.seed_hi, p.rk);
     p.tie_tick = tie_tick_for(h->N);
     { const char *ex = getenv("BS_EXACT_TRIG"); p.exact_trig = ex && ex[0] == '1'; }
     p.r_hit_base = cfg->hit_base_reward; p.r_hit_plane = cfg->hit_plane_reward;
@@ -722,10 +725,14 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     p.ep_log = nullptr; p.ep_cap = 0;
     // every env starts "done" (nothing spawned yet): the first reset / rollout tick spawns it
     std::vector<uint32_t> meta((size_t)n_envs, 1u << 16);
-    CU(cudaMemcpy(p.meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
-    CU(cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&h->cstream, cudaStreamNonBlocking));
-    for (auto &ev : h->chunk_ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    cudaError_t ce2 = cudaMemcpy(p.meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (ce2 == cudaSuccess) ce2 = cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking);
+    if (ce2 == cudaSuccess) ce2 = cudaStreamCreateWithFlags(&h->cstream, cudaStreamNonBlocking);
+    for (auto &ev : h->chunk_ev) if (ce2 == cudaSuccess) ce2 = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (ce2 != cudaSuccess) {   // (a failure this late must not leak the handle and its allocations)
+        bs_destroy(h);
+        return fail(BS_E_CUDA, std::string("bs_create: ") + cudaGetErrorString(ce2));
+    }
     if (const char *hc = getenv("BS_HOST_CHUNKS")) h->host_chunks = atoi(hc) > 15 ? 15 : atoi(hc);
     *out = h;
     return BS_OK;
@@ -761,6 +768,18 @@ static int launch_step(bs_handle *h, const StepArgs &sa, cudaStream_t st) {
     return BS_OK;
 }
 
+// The ring row of (tick t, env e) is (cursor + t*E + e) % capacity.  Two envs of one launch must never share
+// a row (they are written by different warps): that needs capacity >= E, and, once a launch wraps the ring
+// (T*E > capacity), capacity % E == 0 -- then only the SAME env comes back to a row, later ticks overwrite
+// earlier ones in program order and the ring ends up holding the last capacity/E ticks of the launch.
+static int replay_check(const bs_handle *h, const bs_replay *replay, int64_t T) {
+    if (!replay || replay->capacity <= 0) return BS_OK;
+    if (replay->capacity < h->E) return fail(BS_E_INVALID, "replay ring is smaller than n_envs: rows of different envs would collide");
+    if (T * h->E > replay->capacity && replay->capacity % h->E != 0)
+        return fail(BS_E_INVALID, "a launch that wraps the replay ring (T * n_envs > capacity) needs capacity % n_envs == 0");
+    return BS_OK;
+}
+
 static int check_dtype(const bs_handle *h, int dt) {
     if (h->cont) { if (dt != BS_ACT_F32 && dt != BS_ACT_F64) return fail(BS_E_INVALID, "continuous env takes BS_ACT_F32 or BS_ACT_F64 actions"); }
     else if (dt != BS_ACT_I32 && dt != BS_ACT_F32) return fail(BS_E_INVALID, "discrete env takes BS_ACT_I32 or BS_ACT_F32 (logits) actions");
@@ -787,6 +806,7 @@ int bs_step_team_replay(bs_handle *h, int learner_team, const void *team_actions
     if (other_policy < BS_POL_RANDOM || other_policy > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "other_policy must be an in-kernel policy");
     if (cursor < 0) return fail(BS_E_INVALID, "cursor must be >= 0");
     int rc = check_dtype(h, action_dtype); if (rc) return rc;
+    if ((rc = replay_check(h, replay, 1))) return rc;
     DeviceGuard guard(h->device);
     StepArgs sa{team_actions, action_dtype, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, draws, obs, rew, done, env_done, winner, {}, 0, auto_reset ? 1 : 0};
     sa.pol[1 - learner_team] = other_policy;
@@ -815,9 +835,10 @@ int bs_instinct_actions(bs_handle *h, int team, const float *obs, const double *
 }
 
 static int rollout_check(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue, const void *ext_actions,
-                         int64_t cursor) {
+                         const bs_replay *replay, int64_t cursor) {
     if (!h) return fail(BS_E_INVALID, "null handle");
     if (T < 1) return fail(BS_E_INVALID, "T must be >= 1");
+    { int rc = replay_check(h, replay, T); if (rc) return rc; }
     if (learner_team != 0 && learner_team != 1) return fail(BS_E_INVALID, "learner_team must be 0 (red) or 1 (blue)");
     const int pol[2] = {policy_red, policy_blue};
     for (int t = 0; t < 2; ++t) {
@@ -850,7 +871,7 @@ static int rollout_range(bs_handle *h, int T, int learner_team, int policy_red, 
 
 int bs_rollout_fused(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue, const float *ext_actions,
                      const bs_replay *replay, int64_t cursor, void *stream) {
-    int rc = rollout_check(h, T, learner_team, policy_red, policy_blue, ext_actions, cursor); if (rc) return rc;
+    int rc = rollout_check(h, T, learner_team, policy_red, policy_blue, ext_actions, replay, cursor); if (rc) return rc;
     DeviceGuard guard(h->device);
     return rollout_range(h, T, learner_team, policy_red, policy_blue, ext_actions, replay, cursor, 0, h->E, (cudaStream_t)stream);
 }
@@ -872,6 +893,7 @@ int bs_rollout_actor(bs_handle *h, int T, int learner_team, const bs_actor *acto
     ActorArgs aa;
     int rc = actor_args(h, learner_team, actors, hidden, obs, noise, act_scratch, &aa); if (rc) return rc;
     if (other_policy < BS_POL_RANDOM || other_policy > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "other_policy must be an in-kernel policy");
+    if ((rc = replay_check(h, replay, T))) return rc;
     DeviceGuard guard(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     StepArgs sa{act_scratch, BS_ACT_F32, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, nullptr, obs, rew, done, env_done, winner, {}, 0, 1};
@@ -1039,9 +1061,12 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     std::vector<uint2> pool((size_t)h->W * POOL_CAP);
     std::vector<int> pcnt((size_t)h->W, 0);
     // the observation tables (and the packed 11/10-bit plane words) cover on-field points only
-    for (size_t a = 0; a < EP; ++a)
+    for (size_t a = 0; a < EP; ++a) {
         if (v->plane_x[a] < 0 || v->plane_x[a] > 1200 || v->plane_y[a] < 0 || v->plane_y[a] > 800)
             return fail(BS_E_INVALID, "bs_set_state: plane position outside the 1200x800 field");
+        if (!(v->plane_dir[a] >= 0.0 && v->plane_dir[a] <= 360.0))   // Plane.rotate keeps it there, sprites.py:100-103
+            return fail(BS_E_INVALID, "bs_set_state: plane direction outside [0, 360]");
+    }
     for (size_t q = 0; q < (size_t)E * 2; ++q)
         if (v->base_pos[q * 2] < 0 || v->base_pos[q * 2] > 1200 || v->base_pos[q * 2 + 1] < 0 || v->base_pos[q * 2 + 1] > 800)
             return fail(BS_E_INVALID, "bs_set_state: base position outside the 1200x800 field");
@@ -1183,8 +1208,7 @@ int bs_instinct_actions_host(bs_handle *h, int team, const float *obs, const dou
 // T, cudaMemcpy2DAsync on the copy stream) while chunk k's rollout runs on the compute stream.
 int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
                           const float *ext_actions, const bs_replay *replay, int64_t cursor, int64_t stats_out[8]) {
-    int rc = rollout_check(h, T, learner_team, policy_red, policy_blue,
-                           ext_actions ? (const void *)ext_actions : (const void *)h, cursor);
+    int rc = rollout_check(h, T, learner_team, policy_red, policy_blue, ext_actions, replay, cursor);  // (BS_POL_EXTERNAL without actions: BS_E_INVALID)
     if (rc) return rc;
     DeviceGuard guard(h->device);
     if (!ext_actions) {

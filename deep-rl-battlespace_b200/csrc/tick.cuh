@@ -42,6 +42,8 @@ struct Params {
     long long W;          // warps = ceil(E / K), K = 32 / 2N envs per warp
     long long env_offset; // global index of env 0 (sharding)
     uint32_t seed_lo, seed_hi;
+    uint32_t rk[20];      // Philox round keys (seed + r * Weyl constants), filled by philox_round_keys(): constant-bank
+                          // operands of the round XORs instead of two integer adds per round
     int tie_tick;         // first step call whose accumulated 0.1s reach 10+2N (battle_env.py:316-319)
     int exact_trig;       // BS_EXACT_TRIG=1 at bs_create: never speculate in fp32 (cos_sin_fast); for the parity test
     double r_hit_base, r_hit_plane, r_miss, r_die, r_lose;
@@ -90,12 +92,26 @@ static __device__ PHILOX_INLINE uint4 philox4x32_10(uint32_t c0, uint32_t c1, ui
     return make_uint4(c0, c1, c2, c3);
 }
 
+// the same generator with the ten round keys taken from the kernel parameters (rk[2r], rk[2r+1])
+__device__ __forceinline__ uint4 philox4x32_10_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const uint32_t (&rk)[20]) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const unsigned long long p0 = (unsigned long long)0xD2511F53u * c0, p1 = (unsigned long long)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ rk[2 * r], n2 = (uint32_t)(p0 >> 32) ^ c3 ^ rk[2 * r + 1];
+        c0 = n0; c1 = (uint32_t)p1; c2 = n2; c3 = (uint32_t)p0;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+inline void philox_round_keys(uint32_t seed_lo, uint32_t seed_hi, uint32_t (&rk)[20]) {
+    for (int r = 0; r < 10; ++r) { rk[2 * r] = seed_lo + (uint32_t)r * 0x9E3779B9u; rk[2 * r + 1] = seed_hi + (uint32_t)r * 0xBB67AE85u; }
+}
+
 __device__ __forceinline__ void env_philox(const Params &p, long long e, uint32_t episode, int tick,
                                            int agent, int purpose, uint32_t (&w)[4]) {
     unsigned long long g = (unsigned long long)(p.env_offset + e);
-    uint4 r = philox4x32_10((uint32_t)g, (uint32_t)(g >> 32), episode,
-                            ((uint32_t)tick << 16) | ((uint32_t)agent << 8) | (uint32_t)purpose,
-                            p.seed_lo, p.seed_hi);
+    uint4 r = philox4x32_10_rk((uint32_t)g, (uint32_t)(g >> 32), episode,
+                               ((uint32_t)tick << 16) | ((uint32_t)agent << 8) | (uint32_t)purpose, p.rk);
     w[0] = r.x; w[1] = r.y; w[2] = r.z; w[3] = r.w;
 }
 
@@ -223,7 +239,9 @@ __device__ __forceinline__ float pair_angle(double r0, bool neg, double a0) {
     if (r < 0) r += TWO_PI;
     const double t = 360 - r * RAD2DEG;
     double rel = 180 + a0 - t;
-    if (rel < -180) rel += 360;
+    // `if angle < -180: angle += 360` (battle_env.py:49) can never fire here: a plane's direction stays in
+    // [0, 360] (Plane.rotate, sprites.py:100-103; bs_set_state rejects anything else), so 180 + a0 >= 180
+    // exactly, and t <= 360 exactly (r >= 0), hence rel >= -180.  Only the upper wrap is left.
     if (rel > 180) rel -= 360;
     return div360_f32(rel);
 }
@@ -286,14 +304,15 @@ __device__ __forceinline__ void instinct(const float (&o)[3 * N + 2], double sho
         double a2 = 0;
         if (td < 500.0 / 3 * 2 && fabs(ta) < 20) a2 = shoot_u < 0.6 ? 1.0 : -1.0;
         double a0 = div_const(td, DIAG, 1.0 / DIAG) * 2 - 1;
-        double v = div_const(-ta, 35.0, 1.0 / 35.0), a1;
-        if (ta > 0) a1 = v > -1 ? v : -1; else a1 = v < 1 ? v : 1;
-        double t0 = a0 + (-0.15 + (0.15 - -0.15) * n0);
-        double t1 = a1 + (-0.15 + (0.15 - -0.15) * n1);
-        double t2 = a2 + (-0.15 + (0.15 - -0.15) * n2);
-        a[0] = t0 < -1 ? -1 : (t0 > 1 ? 1 : t0);
-        a[1] = t1 < -1 ? -1 : (t1 > 1 ? 1 : t1);
-        a[2] = t2 < -1 ? -1 : (t2 > 1 ? 1 : t2);
+        // agent.py:47-50: max(v, -1) when ang > 0 (v < 0), min(v, 1) otherwise (v >= 0): one clamp covers both
+        // (no NaN can occur; fmax/fmin keep the sign of a zero like the reference's comparisons do)
+        const double v = div_const(-ta, 35.0, 1.0 / 35.0), a1 = fmin(fmax(v, -1.0), 1.0);
+        const double t0 = a0 + (-0.15 + (0.15 - -0.15) * n0);
+        const double t1 = a1 + (-0.15 + (0.15 - -0.15) * n1);
+        const double t2 = a2 + (-0.15 + (0.15 - -0.15) * n2);
+        a[0] = fmin(fmax(t0, -1.0), 1.0);   // np.clip, agent.py:54
+        a[1] = fmin(fmax(t1, -1.0), 1.0);
+        a[2] = fmin(fmax(t2, -1.0), 1.0);
         adisc = 0;
     } else {
         adisc = (td < 500.0 / 2 && fabs(ta) < 20) ? 1 : (ta > 0 ? 3 : 2);
@@ -472,13 +491,12 @@ __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lan
 // (-1,0) is 0, the C cast in pygame's Rect setter).
 __device__ __forceinline__ bool bullet_advance(uint32_t &P, int32_t dlt, int age) {
     P += (uint32_t)dlt;
-    uint32_t Q = (P & B_POS) - B_BIAS;  // fields x, y
-    bool miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
-    if (miss) {
-        if ((Q & 0xffffu) == 0xffffu && !(P & B_XEXACT)) { P += 1u; Q += 1u; }
-        if ((Q >> 16) == 0xffffu && !(P & B_YEXACT)) { P += 0x10000u; Q += 0x10000u; }
-        miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
-    }
+    // a biased field of 63 is a coordinate of -1; unless the step is an exact integer it came from a sum in
+    // (-1, 0), which the C cast turns into 0.  Branch-free (two compares on the packed word).
+    if ((P & (0xffffu | B_XEXACT)) == 63u) P += 1u;
+    if ((P & (0x1fff0000u | B_YEXACT)) == (63u << 16)) P += 0x10000u;
+    const uint32_t Q = (P & B_POS) - B_BIAS;  // fields x, y (a negative one wraps to a huge unsigned value)
+    const bool miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
     return miss || age >= SLOTS;  // 12th update: dist_travelled >= 500, sprites.py:334-337
 }
 
@@ -528,8 +546,9 @@ __device__ __forceinline__ void resolve_plane_hits(const Geo<N> &g, Lane<N> &s, 
 constexpr int WARPS = BLOCK / 32;
 constexpr int POOL_CAP = 32 * SLOTS;  // <= 11 survivors + 1 spawn per lane at the start of a pass
 struct WarpPool {
-    uint32_t pos[POOL_CAP], meta[POOL_CAP];
+    uint2 ent[POOL_CAP];         // .x = pos word, .y = meta word: the HBM layout, moved with 64-bit accesses
     uint32_t ev[32], cand[32];   // per owner lane: event codes / candidate ages of this tick
+    uint32_t hits[32];           // per plane lane: bullets whose first overlapped plane (alive at the start of the loop) it is
     uint32_t candt[SLOTS][32];   // per (age index, owner): pool index << 8 | overlap mask
     uint32_t plane[32];          // x | y << 16 of every lane's plane after the move (0x7fff7fff: not alive)
     uint32_t baseT[32];          // enemy-base test word | first lane of the enemy team << 27
@@ -545,21 +564,18 @@ __device__ __forceinline__ void pool_publish_base(const Geo<N> &g, const Lane<N>
     w.baseT[g.lane] = ((((uint32_t)(s.ebx - 33)) | ((uint32_t)(s.eby - 32) << 16)) + B_BIAS) | ((uint32_t)g.eb << 27);
 }
 
-// kill: this lane's env was reset at the top of this tick (its old bullets vanish, battle_env.py:272).
+// The bullets of an env that is reset vanish (self.bullets = [], battle_env.py:272): the callers drop them
+// with pool_filter() when that happens (once per game), which keeps the per-tick loop free of that test.
 template <int N>
 __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpPool &w, int &cnt, const TickCtx &c,
-                                              bool kill, unsigned &ev, int &died_ai) {
+                                              unsigned &ev, int &died_ai) {
     const int lane = g.lane;
     const unsigned lt = (1u << lane) - 1u;
     // a plane that is not in self.agents is published far off the field: every rect test against it fails
     w.plane[lane] = s.hp > 0 ? ((uint32_t)s.x | ((uint32_t)s.y << 16)) : 0x7fff7fffu;
-    const unsigned runmask = __ballot_sync(FULL, c.run), killmask = __ballot_sync(FULL, kill);
+    const unsigned runmask = __ballot_sync(FULL, c.run);
     const unsigned sp = __ballot_sync(FULL, c.spawnP != 0);
-    if (c.spawnP) {
-        const int idx = cnt + __popc(sp & lt);
-        w.pos[idx] = c.spawnP;
-        w.meta[idx] = pack_meta(c.spawnD, lane, 0);
-    }
+    if (c.spawnP) w.ent[cnt + __popc(sp & lt)] = make_uint2(c.spawnP, pack_meta(c.spawnD, lane, 0));
     const int cnt_in = cnt + __popc(sp);
     __syncwarp();
     // (the caller has run gather(): enemy positions after the move, hp before the bullet loop)
@@ -567,17 +583,15 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
 #pragma unroll 1
     for (int base = 0; base < cnt_in; base += 32) {
         const int idx = base + lane;
-        uint32_t P = 0, M = 0;
-        if (idx < cnt_in) { P = w.pos[idx]; M = w.meta[idx]; }
+        uint2 en = make_uint2(0u, 0u);
+        if (idx < cnt_in) en = w.ent[idx];
+        uint32_t P = en.x, M = en.y;
         const int owner = (M >> 23) & 31;
         const int age = (int)(M >> 28) + 1;             // updates including this one
         const int ai = SLOTS - age;                     // age index, 0 = oldest
-        const bool live = (P & B_VALID) != 0;
-        const bool killed = killmask != 0 && ((killmask >> owner) & 1u) && age >= 2;  // (killmask: warp-uniform, rarely set)
-        const bool moves = live && !killed && ((runmask >> owner) & 1u);
-        bool keep = live && !killed;
+        bool keep = (P & B_VALID) != 0;                 // dead entries (plane hits of the last tick) are squeezed out
         unsigned cm = 0;
-        if (moves) {
+        if (keep && ((runmask >> owner) & 1u)) {        // the bullets of an env that did not run this tick stay put
             const uint32_t bt = w.baseT[owner];
             unsigned code = 0;
             if (bullet_advance(P, meta_dlt(M), age)) code = 1u;
@@ -590,13 +604,14 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
                     cm |= (rect_hit(Pp - w.plane[eb + j], 55u, 50u) ? 1u : 0u) << j;
                 }
                 M += 1u << 28;
+                if (cm) atomicAdd(&w.hits[eb + __ffs(cm) - 1], 1u);
             }
             if (code) { atomicOr(&w.ev[owner], code << (2 * ai)); keep = false; }
         }
         const unsigned kb = __ballot_sync(FULL, keep);
         const int nidx = out + __popc(kb & lt);
         if (keep) {
-            w.pos[nidx] = P; w.meta[nidx] = M;
+            w.ent[nidx] = make_uint2(P, M);             // nidx <= idx: never ahead of a read
             if (cm) { atomicOr(&w.cand[owner], 1u << ai); w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm; }
         }
         out += __popc(kb);
@@ -605,11 +620,26 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
     __syncwarp();
     ev = w.ev[lane];
     const unsigned cand = w.cand[lane];
-    w.ev[lane] = 0; w.cand[lane] = 0;
+    const int nh = (int)w.hits[lane];
+    w.ev[lane] = 0; w.cand[lane] = 0; w.hits[lane] = 0;
     died_ai = -1;
-    resolve_plane_hits<N>(g, s, cand, ev, died_ai,
-        [&](int ai) { return w.candt[ai][lane] & 0xffu; },
-        [&](int ai) { w.pos[w.candt[ai][lane] >> 8] = 0; });
+    // Phase 2.  The order of the list only matters when a plane can die inside this tick: if every plane is
+    // overlapped by fewer bullets than it has hit points, self.agents does not change during the loop and
+    // every candidate hits the first plane it overlaps (battle_env.py:348-360), whatever the order.
+    if (!__any_sync(FULL, s.hp > 0 && nh >= s.hp)) {
+        s.hp -= nh;                                     // (stays > 0; a dead plane collects no hits: it is off the field)
+        unsigned cc = cand;
+        while (cc) {
+            const int ai = __ffs(cc) - 1;
+            cc &= cc - 1;
+            ev |= 3u << (2 * ai);
+            w.ent[w.candt[ai][lane] >> 8].x = 0;
+        }
+    } else {
+        resolve_plane_hits<N>(g, s, cand, ev, died_ai,
+            [&](int ai) { return w.candt[ai][lane] & 0xffu; },
+            [&](int ai) { w.ent[w.candt[ai][lane] >> 8].x = 0; });
+    }
 }
 
 // HBM <-> shared memory: the pool has the same layout in both, so a launch copies `cnt` packed entries
@@ -627,9 +657,9 @@ __device__ __forceinline__ void pool_load(const Params &p, long long gw, bool wv
     cnt = wvalid ? p.pool_cnt[gw] : 0;
 #pragma unroll
     for (int q = 0; q < POOL_SPEC; ++q)
-        if (q * 32 + lane < cnt) { w.pos[q * 32 + lane] = v[q].x; w.meta[q * 32 + lane] = v[q].y; }
-    for (int idx = POOL_SPEC * 32 + lane; idx < cnt; idx += 32) { const uint2 e = src[idx]; w.pos[idx] = e.x; w.meta[idx] = e.y; }
-    w.ev[lane] = 0; w.cand[lane] = 0;
+        if (q * 32 + lane < cnt) w.ent[q * 32 + lane] = v[q];
+    for (int idx = POOL_SPEC * 32 + lane; idx < cnt; idx += 32) w.ent[idx] = src[idx];
+    w.ev[lane] = 0; w.cand[lane] = 0; w.hits[lane] = 0;
     __syncwarp();
 }
 
@@ -637,7 +667,7 @@ __device__ __forceinline__ void pool_store(const Params &p, long long gw, bool w
     __syncwarp();
     if (!wvalid) return;
     uint2 *dst = p.pool + gw * POOL_CAP;
-    for (int idx = lane; idx < cnt; idx += 32) dst[idx] = make_uint2(w.pos[idx], w.meta[idx]);
+    for (int idx = lane; idx < cnt; idx += 32) dst[idx] = w.ent[idx];
     if (lane == 0) p.pool_cnt[gw] = cnt;
 }
 
@@ -650,11 +680,11 @@ __device__ __forceinline__ void pool_filter(WarpPool &w, int &cnt, unsigned kill
 #pragma unroll 1
     for (int base = 0; base < cnt; base += 32) {
         const int idx = base + lane;
-        uint32_t P = 0, M = 0;
-        if (idx < cnt) { P = w.pos[idx]; M = w.meta[idx]; }
-        const bool keep = (P & B_VALID) != 0 && !((killmask >> ((M >> 23) & 31)) & 1u);
+        uint2 en = make_uint2(0u, 0u);
+        if (idx < cnt) en = w.ent[idx];
+        const bool keep = (en.x & B_VALID) != 0 && !((killmask >> ((en.y >> 23) & 31)) & 1u);
         const unsigned kb = __ballot_sync(FULL, keep);
-        if (keep) { const int n = out + __popc(kb & lt); w.pos[n] = P; w.meta[n] = M; }  // n <= idx: never ahead of a read
+        if (keep) w.ent[out + __popc(kb & lt)] = en;    // never ahead of a read
         out += __popc(kb);
     }
     cnt = out;

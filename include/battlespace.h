@@ -51,7 +51,8 @@
  *       noise_u[k] = (w_k >> 8) / 2^24  (k=0..2)      instinct noise  instinct/agent.py:53
  *       shoot_u    = ((w0&255)<<16 | (w1&255)<<8 | (w2&255)) / 2^24    instinct/agent.py:44
  *       spread_u   = w3 / 2^32                        Bullet spread   envs/sprites.py:314
- *       random policy: continuous a_k = 2*noise_u[k]-1, discrete a = w0 >> 30
+ *       random policy: continuous a_k = 2*noise_u[k]-1, discrete a = w0 >> 30 (= floor(4*noise_u[0]), which is
+ *       what an injected noise_u[0] yields)
  *   purpose 1 (plane spawn, agent = plane): x, y, dir = lo + mulhi(w_k, hi-lo+1)
  *   purpose 2 (base spawn): red x,y from w0,w1; blue x,y from w2,w3
  *   `tick` is the env's step counter before the call, `episode` starts at 1.
@@ -90,7 +91,11 @@ typedef struct bs_config {
     double lose_punishment;
 } bs_config;
 
-/* Replay ring in the row layout of maddpg/buffer.py:11-23 (float32; rows of the learner team). */
+/* Replay ring in the row layout of maddpg/buffer.py:11-23 (float32; rows of the learner team).
+ * The row of (tick t, env e) of a call is (cursor + t*n_envs + e) % capacity.  Rows of different envs must
+ * never collide inside one call: capacity >= n_envs, and a call that wraps the ring (T*n_envs > capacity)
+ * needs capacity % n_envs == 0 -- the ring then keeps the last capacity/n_envs ticks of that call.  Anything
+ * else is answered with BS_E_INVALID. */
 typedef struct bs_replay {
     float *state;       /* [capacity, N*L]   state_mem / actor_states[k] = columns k*L..(k+1)*L */
     float *new_state;   /* [capacity, N*L] */

@@ -90,6 +90,26 @@ def test_c_abi_argument_errors(cuda_device):
     assert lib.bs_rollout_fused(hh, 4, 0, 17, _lib.POL_INSTINCT, nul, nul, C.c_int64(0), nul) == INV and "policy" in msg()
     assert lib.bs_rollout_fused(hh, 4, 0, _lib.POL_EXTERNAL, _lib.POL_INSTINCT, nul, nul, C.c_int64(0), nul) == INV   # no ext_actions
     assert lib.bs_rollout_fused(hh, 4, 0, _lib.POL_RANDOM, _lib.POL_INSTINCT, nul, nul, C.c_int64(-1), nul) == INV and "cursor" in msg()
+    # the host entry point checks the same thing (it used to launch with a null action pointer)
+    assert lib.bs_rollout_fused_host(hh, 4, 0, _lib.POL_EXTERNAL, _lib.POL_INSTINCT, nul, nul, C.c_int64(0), stats) == INV
+    assert "ext_actions" in msg()
+    # replay ring: rows of different envs must never collide inside one launch
+    from battlespace import DeviceReplay
+    small = DeviceReplay(4, 2, 3, 11, 3, env.device)                  # fewer rows than envs (8)
+    rs = small.as_struct()
+    assert lib.bs_rollout_fused(hh, 4, 0, _lib.POL_RANDOM, _lib.POL_INSTINCT, nul, C.byref(rs), C.c_int64(0), nul) == INV
+    assert "smaller than n_envs" in msg()
+    odd = DeviceReplay(20, 2, 3, 11, 3, env.device)                   # 4 x 8 rows wrap a 20-row ring, 20 % 8 != 0
+    ro = odd.as_struct()
+    assert lib.bs_rollout_fused(hh, 4, 0, _lib.POL_RANDOM, _lib.POL_INSTINCT, nul, C.byref(ro), C.c_int64(0), nul) == INV
+    assert "capacity % n_envs" in msg()
+    assert lib.bs_rollout_fused(hh, 2, 0, _lib.POL_RANDOM, _lib.POL_INSTINCT, nul, C.byref(ro), C.c_int64(0), nul) == 0   # 16 rows fit
+    with pytest.raises(ValueError):
+        env.rollout(4, "random", "instinct", 0, None, odd)
+    with pytest.raises(ValueError):                                   # wrong dtype / shape of the learner's action block
+        env.rollout(4, "external", "instinct", 0, torch.zeros(4, 8, 3, 3, dtype=torch.float64, device=env.device))
+    with pytest.raises(ValueError):
+        env.rollout(4, "external", "instinct", 0, torch.zeros(3, 8, 3, 3, device=env.device))
     # single tick: action dtype must fit the action space; null handle
     a = torch.zeros(8, 6, 3, device=env.device)
     assert lib.bs_step(hh, C.c_void_p(a.data_ptr()), _lib.ACT_I32, nul, nul, nul, nul, nul, nul, nul) == INV and "continuous" in msg()
@@ -101,5 +121,5 @@ def test_c_abi_argument_errors(cuda_device):
     assert lib.bs_episode_log(hh, C.c_void_p(buf.data_ptr()), C.c_int64(100)) == INV and "power of two" in msg()
     # a failed call leaves the handle usable
     env.rollout(4, "random", "instinct")
-    assert lib.bs_stats(hh, stats, nul) == 0 and stats[6] == 4 * 8
+    assert lib.bs_stats(hh, stats, nul) == 0 and stats[6] == (4 + 2) * 8
     env.close()
