@@ -345,9 +345,15 @@ def main():
         for _ in range(3):
             env.rollout_host(T, "external", "instinct", 0, host_act, replay)
         barrier()
+        # every step: its action block H2D from pinned memory (bs_rollout_fused_host_begin returns when the block
+        # has been consumed), its kernels, its counters D2H (bs_rollout_fused_host_end); one call stays in flight
+        # so that the copies of step k+1 overlap the kernels of step k
         t0 = time.perf_counter()
-        for _ in range(k_e2e):
-            env.rollout_host(T, "external", "instinct", 0, host_act, replay)   # H2D + kernel + D2H, synchronous
+        env.rollout_host_begin(T, "external", "instinct", 0, host_act, replay)
+        for _ in range(k_e2e - 1):
+            env.rollout_host_begin(T, "external", "instinct", 0, host_act, replay)
+            env.rollout_host_end()
+        env.rollout_host_end()
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
@@ -355,7 +361,8 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e = {"value": k_e2e * T * E * 2 * N * world / float(tt.item()), "unit": UNIT,
                "h2d_bytes_per_step": T * E * N * A * 4, "d2h_bytes_per_step": 64, "steps": k_e2e,
-               "call": "bs_rollout_fused_host (red actions [T,E,3,3] f32 from pinned host memory, counters back)",
+               "call": "bs_rollout_fused_host_begin/_end, one call in flight (red actions [T,E,3,3] f32 from pinned host "
+                       "memory every step, the 8 counters back every step)",
                "host_numa_bound": bool(near), "cpus": len(mine) if mine else None}
         del host_act
         step_e2e = step_host_e2e(env, N, E, world, dist, dev)

@@ -24,7 +24,7 @@ SYMBOLS = (
     "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_reset", "bs_step", "bs_step_team",
     "bs_step_team_replay", "bs_instinct_actions", "bs_rollout_fused", "bs_stats", "bs_stats_device", "bs_get_state",
     "bs_set_state", "bs_reset_host", "bs_step_host", "bs_step_team_host", "bs_instinct_actions_host",
-    "bs_rollout_fused_host", "bs_actor_forward", "bs_rollout_actor", "bs_replay_sample", "bs_render", "bs_episode_log", "bs_episode_log_count",
+    "bs_rollout_fused_host", "bs_rollout_fused_host_begin", "bs_rollout_fused_host_end", "bs_actor_forward", "bs_rollout_actor", "bs_replay_sample", "bs_render", "bs_episode_log", "bs_episode_log_count",
 )
 
 
@@ -98,6 +98,8 @@ lib.bs_step_host.argtypes = [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_step_team_host.argtypes = [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_instinct_actions_host.argtypes = [_vp, _i, _vp, _vp, _vp]
 lib.bs_rollout_fused_host.argtypes = [_vp, _i, _i, _i, _i, _vp, C.POINTER(bs_replay), _i64, _vp]
+lib.bs_rollout_fused_host_begin.argtypes = [_vp, _i, _i, _i, _i, _vp, C.POINTER(bs_replay), _i64]
+lib.bs_rollout_fused_host_end.argtypes = [_vp, _vp]
 lib.bs_actor_forward.argtypes = [_vp, _i, C.POINTER(bs_actor), _i, _vp, C.POINTER(bs_ou_noise), _vp, _vp]
 lib.bs_rollout_actor.argtypes = [_vp, _i, _i, C.POINTER(bs_actor), _i, _i, C.POINTER(bs_ou_noise), C.POINTER(bs_replay), _i64,
                                  _vp, _vp, _vp, _vp, _vp, _vp, _vp]

@@ -412,6 +412,34 @@ class parallel_env:
             replay.mem_cntr += int(T) * self._E
         return out
 
+    def rollout_host_begin(self, T, red="random", blue="instinct", learner_team=0, ext_actions_host=None, replay=None,
+                           cursor=None):
+        """First phase of ``rollout_host``: returns once ``ext_actions_host`` has been copied to the device (the
+        caller may refill it for the next call while the kernels run).  Pair with ``rollout_host_end``; at most
+        two calls may be in flight."""
+        self._check_ext_actions(T, ext_actions_host, False)
+        self._check_replay(replay, T)
+        if getattr(self, "_host_inflight", 0) == 0:
+            self._host_call_barrier()
+        rp = None
+        if replay is not None:
+            rp = replay.as_struct()
+            if cursor is None:
+                cursor = replay.mem_cntr
+        check(lib.bs_rollout_fused_host_begin(self._h, int(T), int(learner_team), POLICIES[red], POLICIES[blue],
+                                              _ptr(ext_actions_host), C.byref(rp) if rp is not None else None,
+                                              int(cursor or 0)))
+        self._host_inflight = getattr(self, "_host_inflight", 0) + 1
+        if replay is not None:
+            replay.mem_cntr += int(T) * self._E
+
+    def rollout_host_end(self):
+        """Second phase: waits for the oldest call in flight, returns the 8 counters as they stood after it."""
+        out = np.zeros(8, np.int64)
+        check(lib.bs_rollout_fused_host_end(self._h, _np_ptr(out)))
+        self._host_inflight -= 1
+        return out
+
     # ----- learner team's actors in CUDA (SURVEY 8 f1) -----------------------------------------------
     def actor_actions(self, actors, team=0, obs=None, noise=None, normals=None, reset_mask=None, out=None):
         """Batched ``Team.choose_actions`` (maddpg/team.py:21-28): float32 [E,N,A] actions of ``team``'s

@@ -99,7 +99,7 @@ __device__ __forceinline__ void init_bias(float (&acc)[8][8], const float *b, in
 }
 
 // relu(LayerNorm(row)) for the 8 rows of the thread's block, then staged as H[col][row]
-__device__ __forceinline__ void ln_relu_store(float (&acc)[8][8], const float *g, const float *b, float *H, int tc, int tr) {
+__device__ __forceinline__ void ln_relu_store(float (&acc)[8][8], const float *g, const float *b, float *H, int tc, int rq) {
     const float4 glo = lds4(g + tc * 4), ghi = lds4(g + 32 + tc * 4), blo = lds4(b + tc * 4), bhi = lds4(b + 32 + tc * 4);
     const float gg[8] = {glo.x, glo.y, glo.z, glo.w, ghi.x, ghi.y, ghi.z, ghi.w};
     const float bb[8] = {blo.x, blo.y, blo.z, blo.w, bhi.x, bhi.y, bhi.z, bhi.w};
@@ -136,8 +136,8 @@ __device__ __forceinline__ void ln_relu_store(float (&acc)[8][8], const float *g
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         const int col = (c < 4 ? 0 : 28) + tc * 4 + c;  // columns tc*4..+3 and 32+tc*4..+3
-        *reinterpret_cast<float4 *>(H + col * HP + tr * 4) = make_float4(acc[0][c], acc[1][c], acc[2][c], acc[3][c]);
-        *reinterpret_cast<float4 *>(H + col * HP + 64 + tr * 4) = make_float4(acc[4][c], acc[5][c], acc[6][c], acc[7][c]);
+        *reinterpret_cast<float4 *>(H + col * HP + rq) = make_float4(acc[0][c], acc[1][c], acc[2][c], acc[3][c]);
+        *reinterpret_cast<float4 *>(H + col * HP + rq + 16) = make_float4(acc[4][c], acc[5][c], acc[6][c], acc[7][c]);
     }
 }
 
@@ -147,7 +147,13 @@ __global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
     extern __shared__ float4 smem4[];
     float *sm = reinterpret_cast<float *>(smem4);
     const int tid = threadIdx.x, k = blockIdx.y;
-    const int tc = tid & 7, tr = tid >> 3;  // column group (8 per row group), row group (16)
+    // Thread tile: column group tc (columns tc*4..+3 and 32+tc*4..+3) x row group: two quads of rows.  Each WARP
+    // owns 32 consecutive rows of the tile (rows rq..rq+3 and rq+16..rq+19 per thread), so the activations it
+    // stages between the layers are private to it and the tile loop needs no block barrier, only __syncwarp():
+    // the four warps of a block drift apart and hide each other's LayerNorm / head phases (r1j: 4 __syncthreads
+    // per tile at 12 resident warps left the issue slots 57 % busy).
+    const int tc = tid & 7;
+    const int rq = (tid & ~31) + ((tid >> 3) & 3) * 4;   // first row of the thread's first quad; second quad at rq + 16
     const ActorNet net = aa.net[k];
 
     // ---- actor k's parameters -> shared memory, transposed to [in][out] --------------------------
@@ -169,7 +175,7 @@ __global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
     coop_copy(sm + S::B2, net.fc2_b, AH); coop_copy(sm + S::G2, net.ln2_g, AH); coop_copy(sm + S::E2, net.ln2_b, AH);
     if (tid < 4) sm[S::B3 + tid] = tid < A ? __ldg(net.pi_b + tid) : 0.0f;
     float *Os = sm + S::OS, *H = sm + S::H;
-    const float *arow = H + tr * 4, *wcol1 = sm + S::W1T + tc * 4, *wcol2 = sm + S::W2T + tc * 4;
+    const float *arow = H + rq, *wcol1 = sm + S::W1T + tc * 4, *wcol2 = sm + S::W2T + tc * 4;
 
     const long long tiles = (aa.E + TM - 1) / TM;
     // The next tile's observation row is fetched into registers while the current tile computes.
@@ -186,29 +192,30 @@ __global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;");
     fetch(blockIdx.x);
+    __syncthreads();      // parameters staged (the only block barrier)
     for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const long long e = tile * TM + tid;
         const bool ok = e < aa.E;
 #pragma unroll
         for (int c = 0; c < L; ++c) Os[c * TM + tid] = onext[c];
-        __syncthreads();  // obs tile staged (first pass: parameters too); H of the previous tile is free
+        __syncwarp();     // the warp's 32 obs rows are staged; its H rows of the previous tile are free
         fetch(tile + gridDim.x);
         float acc[8][8];
         // ---- fc1 -----------------------------------------------------------------------------------
         init_bias(acc, sm + S::B1, tc);
 #pragma unroll
         for (int c = 0; c < L; ++c)
-            outer8x8(acc, lds4(Os + c * TM + tr * 4), lds4(Os + c * TM + 64 + tr * 4), lds4(wcol1 + c * WP), lds4(wcol1 + c * WP + 32));
-        ln_relu_store(acc, sm + S::G1, sm + S::E1, H, tc, tr);
-        __syncthreads();
+            outer8x8(acc, lds4(Os + c * TM + rq), lds4(Os + c * TM + rq + 16), lds4(wcol1 + c * WP), lds4(wcol1 + c * WP + 32));
+        ln_relu_store(acc, sm + S::G1, sm + S::E1, H, tc, rq);
+        __syncwarp();
         // ---- fc2 -----------------------------------------------------------------------------------
         init_bias(acc, sm + S::B2, tc);
 #pragma unroll 8
         for (int c = 0; c < AH; ++c)
-            outer8x8(acc, lds4(arow + c * HP), lds4(arow + c * HP + 64), lds4(wcol2 + c * WP), lds4(wcol2 + c * WP + 32));
-        __syncthreads();  // every thread has read h1 before it is overwritten by h2
-        ln_relu_store(acc, sm + S::G2, sm + S::E2, H, tc, tr);
-        __syncthreads();
+            outer8x8(acc, lds4(arow + c * HP), lds4(arow + c * HP + 16), lds4(wcol2 + c * WP), lds4(wcol2 + c * WP + 32));
+        __syncwarp();     // every lane has read h1 before it is overwritten by h2
+        ln_relu_store(acc, sm + S::G2, sm + S::E2, H, tc, rq);
+        __syncwarp();
         // ---- pi + tanh (+ OU noise, clamp): one row per thread -------------------------------------
         float pi[4];
 #pragma unroll

@@ -29,7 +29,7 @@ __device__ __forceinline__ long long global_warp() {
     return ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 }
 
-__device__ __forceinline__ double clip1(double v) { return v < -1 ? -1 : (v > 1 ? 1 : v); }  // battle_env.py:295-297
+__device__ __forceinline__ double clip1(double v) { return clamp1(v); }  // np.clip(value, -1, 1), battle_env.py:295-297
 
 __device__ __forceinline__ int argmax4(const float *v) {  // np.argmax: first maximum, battle_env.py:328
     int b = 0;
@@ -49,24 +49,24 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(Params p, const uint8_t *m
     Lane<N> s;
     double ret0, ret1;
     load_lane(p, g, s, ret0, ret1);
-    const bool need = g.valid && (mask == nullptr || mask[g.e] != 0);
+    const bool need = g.valid() && (mask == nullptr || mask[g.e()] != 0);
     if (need) {
-        reset_lane(p, g, s, draws != nullptr, draws ? draws + g.e * (4 + 6 * N) : nullptr);
+        reset_lane(p, g, s, draws != nullptr, draws ? draws + g.e() * (4 + 6 * N) : nullptr);
         ret0 = ret1 = 0;
     }
     const unsigned killmask = __ballot_sync(FULL, need);
     if (killmask) {  // self.bullets = [] for the envs that were reset, battle_env.py:272
         int cnt;
-        pool_load(p, gw, gw < p.W, g.lane, w, cnt);
-        pool_filter(w, cnt, killmask, g.lane);
-        pool_store(p, gw, gw < p.W, g.lane, w, cnt);
+        pool_load(p, gw, gw < p.W, g.lane(), w, cnt);
+        pool_filter(w, cnt, killmask, g.lane());
+        pool_store(p, gw, gw < p.W, g.lane(), w, cnt);
     }
     gather(g, s);
     if (obs != nullptr) {
         float o[L];
         observe<N>(p, s, o);
-        if (g.valid) {
-            float *dst = obs + (g.e * P + g.i) * L;
+        if (g.valid()) {
+            float *dst = obs + (g.e() * P + g.i()) * L;
 #pragma unroll
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
@@ -103,7 +103,7 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
 #pragma unroll
         for (int c = 0; c < 5; ++c) u[c] = draws_row[c];
     } else {
-        env_philox(p, g.e, s.episode, s.tick, g.i, PURPOSE_AGENT_TICK, w);
+        env_philox(p, g.e(), s.episode, s.tick, g.i(), PURPOSE_AGENT_TICK, w);
         agent_tick_units(w, u);
     }
     spread_u = u[4];
@@ -120,6 +120,39 @@ __device__ __forceinline__ void lane_policy(const Params &p, const Geo<N> &g, co
         }
     } else if (pol == POL_INSTINCT || pol == POL_INSTINCT_FF) {
         instinct<N, CONT>(o, u[0], u[1], u[2], u[3], adisc, a);
+        if (CONT) {
+            if (pol == POL_INSTINCT_FF) a[2] = 1.0;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) raw[c] = (float)a[c];
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) raw[c] = c == adisc ? 1.0f : 0.0f;
+        }
+    }
+}
+
+// The same for the fused rollout, where the draws are always Philox: the uniform policy's actions 2u - 1 come
+// straight from the 24-bit integers (sym24) and only the units a policy consumes are built.
+template <int N, bool CONT>
+__device__ __forceinline__ void lane_policy_philox(const Params &p, const Geo<N> &g, const Lane<N> &s, int pol,
+                                                   const float (&o)[3 * N + 2], int &adisc, double (&a)[3],
+                                                   double &spread_u, float (&raw)[4]) {
+    uint32_t w[4];
+    env_philox(p, g.e(), s.episode, s.tick, g.i(), PURPOSE_AGENT_TICK, w);
+    spread_u = unit32(w[3]);
+    if (pol == POL_RANDOM) {
+        if (CONT) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { a[c] = sym24(w[c] >> 8); raw[c] = (float)a[c]; }
+            adisc = 0;
+        } else {
+            adisc = (int)(w[0] >> 30);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) raw[c] = c == adisc ? 1.0f : 0.0f;
+        }
+    } else if (pol == POL_INSTINCT || pol == POL_INSTINCT_FF) {
+        const double shoot_u = unit24(((w[0] & 0xffu) << 16) | ((w[1] & 0xffu) << 8) | (w[2] & 0xffu));
+        instinct<N, CONT>(o, shoot_u, unit24(w[0] >> 8), unit24(w[1] >> 8), unit24(w[2] >> 8), adisc, a);
         if (CONT) {
             if (pol == POL_INSTINCT_FF) a[2] = 1.0;
 #pragma unroll
@@ -154,18 +187,18 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     asm volatile("griddepcontrol.launch_dependents;");
     load_lane(p, g, s, ret0, ret1);
     int cnt;
-    pool_load(p, gw, gw < p.W, g.lane, w, cnt);
+    pool_load(p, gw, gw < p.W, g.lane(), w, cnt);
     pool_publish_base<N>(g, s, w);
 
     float o[L];
-    const bool writer = g.valid && sa.rp.capacity > 0 && g.team == sa.act_team;
+    const bool writer = g.valid() && sa.rp.capacity > 0 && g.team() == sa.act_team;
     long long row = 0;
-    if (sa.rp.capacity > 0) row = (sa.cursor_mod + g.e % sa.rp.capacity) % sa.rp.capacity;
+    if (sa.rp.capacity > 0) row = (sa.cursor_mod + g.e() % sa.rp.capacity) % sa.rp.capacity;
     const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT || sa.rp.capacity > 0;  // kernel-uniform
     if (need_obs && sa.obs_in != nullptr) {
-        const float *src = sa.obs_in + ((g.valid ? g.e : 0) * P + g.i) * L;
+        const float *src = sa.obs_in + ((g.valid() ? g.e() : 0) * P + g.i()) * L;
 #pragma unroll
-        for (int c = 0; c < L; ++c) o[c] = g.valid ? src[c] : -1.0f;
+        for (int c = 0; c < L; ++c) o[c] = g.valid() ? src[c] : -1.0f;
     } else if (need_obs) { gather(g, s); observe<N>(p, s, o); }
     else {
 #pragma unroll
@@ -173,13 +206,13 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     }
 
     // external actions
-    const int pol = g.team ? sa.pol[1] : sa.pol[0];  // (a dynamic index would make the compiler copy the parameter struct to local memory)
-    const bool ext = g.valid && pol == POL_EXTERNAL && sa.dtype != ACT_NONE;
+    const int pol = g.team() ? sa.pol[1] : sa.pol[0];  // (a dynamic index would make the compiler copy the parameter struct to local memory)
+    const bool ext = g.valid() && pol == POL_EXTERNAL && sa.dtype != ACT_NONE;
     int adisc = 0;
     double a[3] = {0, 0, 0}, spread_u = 0;
     float raw[4] = {0, 0, 0, 0};
     if (ext) {
-        const long long idx = g.e * sa.act_agents + (sa.act_agents == P ? g.i : g.k);
+        const long long idx = g.e() * sa.act_agents + (sa.act_agents == P ? g.i() : g.k());
         if (!CONT) {
             if (sa.dtype == ACT_I32) adisc = ((const int32_t *)sa.actions)[idx];
             else {
@@ -194,8 +227,8 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
             for (int c = 0; c < 3; ++c) a[c] = ((const double *)sa.actions)[idx * 3 + c];
         }
     }
-    if (g.valid) {
-        const double *drow = sa.draws ? sa.draws + (g.e * P + g.i) * 5 : nullptr;
+    if (g.valid()) {
+        const double *drow = sa.draws ? sa.draws + (g.e() * P + g.i()) * 5 : nullptr;
         if (ext) {
             if (!CONT) {
                 if (sa.dtype == ACT_I32) { if (adisc >= 0 && adisc < 4) raw[adisc] = 1.0f; }
@@ -207,7 +240,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
             if (drow) spread_u = drow[4];
             else {
                 uint32_t w[4]; double u[5];
-                env_philox(p, g.e, s.episode, s.tick, g.i, PURPOSE_AGENT_TICK, w);
+                env_philox(p, g.e(), s.episode, s.tick, g.i(), PURPOSE_AGENT_TICK, w);
                 agent_tick_units(w, u);
                 spread_u = u[4];
             }
@@ -223,13 +256,13 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
             for (int c = 0; c < 3; ++c) raw[c] = (float)a[c];
         }
         if (sa.rp.state) {
-            float *dst = sa.rp.state + (row * N + g.k) * L;
+            float *dst = sa.rp.state + (row * N + g.k()) * L;
 #pragma unroll
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
         if (sa.rp.action) {
 #pragma unroll
-            for (int c = 0; c < A; ++c) sa.rp.action[(row * N + g.k) * A + c] = raw[c];
+            for (int c = 0; c < A; ++c) sa.rp.action[(row * N + g.k()) * A + c] = raw[c];
         }
     }
     double rew;
@@ -251,7 +284,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     }
     if (want_obs) {
         if (writer) {
-            const long long ra_i = row * N + g.k;
+            const long long ra_i = row * N + g.k();
             if (sa.rp.new_state) {
                 float *dst = sa.rp.new_state + ra_i * L;
 #pragma unroll
@@ -262,39 +295,39 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
         }
     }
     if (sa.obs != nullptr) {
-        if (g.valid) {
-            float *dst = sa.obs + (g.e * P + g.i) * L;
+        if (g.valid()) {
+            float *dst = sa.obs + (g.e() * P + g.i()) * L;
 #pragma unroll
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
     }
     // auto-reset (the game loop's `env.reset()` for the next game, main.py:148): rewards, dones,
     // env_done and winner below still describe the finished game; obs is the new game's first one.
-    const bool fresh = sa.auto_reset && g.valid && s.env_done;
+    const bool fresh = sa.auto_reset && g.valid() && s.env_done;
     const int out_done = s.env_done, out_hp = s.hp, out_winner = s.winner;
     if (sa.auto_reset && __any_sync(FULL, fresh)) {
         if (fresh) { reset_lane(p, g, s, false, nullptr); ret0 = ret1 = 0; }
-        pool_filter(w, cnt, __ballot_sync(FULL, fresh), g.lane);  // the finished games' bullets vanish, battle_env.py:272
+        pool_filter(w, cnt, __ballot_sync(FULL, fresh), g.lane());  // the finished games' bullets vanish, battle_env.py:272
         gather(g, s);
         float o2[L];
         observe<N>(p, s, o2);
         if (fresh && sa.obs != nullptr) {
-            float *dst = sa.obs + (g.e * P + g.i) * L;
+            float *dst = sa.obs + (g.e() * P + g.i()) * L;
 #pragma unroll
             for (int c = 0; c < L; ++c) dst[c] = o2[c];
         }
     }
-    if (g.valid) {
-        const long long ai = g.e * P + g.i;
+    if (g.valid()) {
+        const long long ai = g.e() * P + g.i();
         if (sa.rew) sa.rew[ai] = (float)rew;
         if (sa.done) sa.done[ai] = (uint8_t)(out_done || out_hp <= 0);  // self.dones, battle_env.py:275,360,478,494
-        if (g.i == 0) {
-            if (sa.env_done) sa.env_done[g.e] = (uint8_t)out_done;
-            if (sa.winner) sa.winner[g.e] = (int8_t)out_winner;
+        if (g.i() == 0) {
+            if (sa.env_done) sa.env_done[g.e()] = (uint8_t)out_done;
+            if (sa.winner) sa.winner[g.e()] = (int8_t)out_winner;
         }
     }
     store_lane(p, g, s, ret0, ret1, sa.auto_reset != 0);
-    pool_store(p, gw, gw < p.W, g.lane, w, cnt);
+    pool_store(p, gw, gw < p.W, g.lane(), w, cnt);
     flush_tally<N>(p, tl);
 }
 
@@ -325,25 +358,27 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
     double ret0, ret1;
     load_lane(p, g, s, ret0, ret1);
     int cnt;
-    pool_load(p, ra.e0 / Geo<N>::K + global_warp(), ra.e0 + global_warp() * Geo<N>::K < ra.e_end, g.lane, w, cnt);  // chunks start on a warp boundary
+    pool_load(p, ra.e0 / Geo<N>::K + global_warp(), ra.e0 + global_warp() * Geo<N>::K < ra.e_end, g.lane(), w, cnt);  // chunks start on a warp boundary
     pool_publish_base<N>(g, s, w);
     gather(g, s);
     float o[L];
     observe<N>(p, s, o);
     Tally tl;
-    const int pol = g.team ? ra.pol[1] : ra.pol[0];  // (a dynamic index would make the compiler copy the parameter struct to local memory:
+    const int pol = g.team() ? ra.pol[1] : ra.pol[0];  // (a dynamic index would make the compiler copy the parameter struct to local memory:
                                                       //  r1o spent 9 % of its stall samples on those reloads)
-    const bool writer = g.valid && g.team == ra.learner && ra.rp.capacity > 0;
-    long long row = 0;
-    if (ra.rp.capacity > 0) row = (ra.cursor_mod + g.e % ra.rp.capacity) % ra.rp.capacity;
+    const bool writer = g.valid() && g.team() == ra.learner && ra.rp.capacity > 0;
+    // ring row of this lane's env at tick t (replay_check: capacity * N < 2^31, so 32-bit indices address every array)
+    uint32_t row = 0;
+    if (ra.rp.capacity > 0) row = (uint32_t)((ra.cursor_mod + g.e() % ra.rp.capacity) % ra.rp.capacity);
+    const uint32_t cap32 = (uint32_t)ra.rp.capacity, emod32 = (uint32_t)ra.e_mod;
 
 #pragma unroll 1
     for (int t = 0; t < ra.T; ++t) {
         // auto-reset: the game loop's env.reset() -- main.py:148
-        const bool need = g.valid && s.env_done;
+        const bool need = g.valid() && s.env_done;
         if (__any_sync(FULL, need)) {
             if (need) { reset_lane(p, g, s, false, nullptr); ret0 = ret1 = 0; pool_publish_base<N>(g, s, w); }
-            pool_filter(w, cnt, __ballot_sync(FULL, need), g.lane);  // the finished games' bullets vanish, battle_env.py:272
+            pool_filter(w, cnt, __ballot_sync(FULL, need), g.lane());  // the finished games' bullets vanish, battle_env.py:272
             gather(g, s);
             float o2[L];
             observe<N>(p, s, o2);
@@ -352,17 +387,18 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
                 for (int c = 0; c < L; ++c) o[c] = o2[c];
             }
         }
+        const uint32_t ra_i = row * N + g.k();   // this plane's slot of the row
         if (writer && ra.rp.state) {
-            float *dst = ra.rp.state + (row * N + g.k) * L;
+            float *dst = ra.rp.state + (size_t)ra_i * L;
 #pragma unroll
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
         int adisc = 0;
         double a[3] = {0, 0, 0}, spread_u = 0;
         float raw[4] = {0, 0, 0, 0};
-        if (g.valid) {
+        if (g.valid()) {
             if (pol == POL_EXTERNAL) {
-                const float *src = ra.ext + (((long long)t * p.E + g.e) * N + g.k) * A;
+                const float *src = ra.ext + (((long long)t * p.E + g.e()) * N + g.k()) * A;
                 if (CONT) {
 #pragma unroll
                     for (int c = 0; c < 3; ++c) { a[c] = clip1((double)src[c]); raw[c] = (float)a[c]; }
@@ -372,15 +408,15 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
                     adisc = argmax4(raw);
                 }
                 uint32_t w4[4]; double u[5];
-                env_philox(p, g.e, s.episode, s.tick, g.i, PURPOSE_AGENT_TICK, w4);
+                env_philox(p, g.e(), s.episode, s.tick, g.i(), PURPOSE_AGENT_TICK, w4);
                 agent_tick_units(w4, u);
                 spread_u = u[4];
             } else {
-                lane_policy<N, CONT>(p, g, s, pol, o, nullptr, adisc, a, spread_u, raw);
+                lane_policy_philox<N, CONT>(p, g, s, pol, o, adisc, a, spread_u, raw);
             }
         }
         if (writer && ra.rp.action) {  // the action row is complete before the tick: write it now
-            float *dst = ra.rp.action + (row * N + g.k) * A;
+            float *dst = ra.rp.action + (size_t)ra_i * A;
 #pragma unroll
             for (int c = 0; c < A; ++c) dst[c] = raw[c];
         }
@@ -397,20 +433,19 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
             observe_finish<N>(s, q, o);
         }
         if (writer) {
-            const long long ra_i = row * N + g.k;
             if (ra.rp.new_state) {
-                float *dst = ra.rp.new_state + ra_i * L;
+                float *dst = ra.rp.new_state + (size_t)ra_i * L;
 #pragma unroll
                 for (int c = 0; c < L; ++c) dst[c] = o[c];
             }
             if (ra.rp.reward) ra.rp.reward[ra_i] = (float)rew;
             if (ra.rp.done) ra.rp.done[ra_i] = (uint8_t)(s.env_done || s.hp <= 0);
         }
-        row += ra.e_mod;
-        if (row >= ra.rp.capacity) row -= ra.rp.capacity;
+        row += emod32;                       // (row, emod32 < capacity <= 2^31 / N: no 32-bit overflow)
+        if (row >= cap32) row -= cap32;
     }
     store_lane(p, g, s, ret0, ret1, true);
-    pool_store(p, ra.e0 / Geo<N>::K + global_warp(), ra.e0 + global_warp() * Geo<N>::K < ra.e_end, g.lane, w, cnt);
+    pool_store(p, ra.e0 / Geo<N>::K + global_warp(), ra.e0 + global_warp() * Geo<N>::K < ra.e_end, g.lane(), w, cnt);
     flush_tally<N>(p, tl);
 }
 
@@ -512,6 +547,12 @@ struct bs_handle {
     cudaStream_t cstream = nullptr;  // copy stream of bs_rollout_fused_host
     cudaEvent_t chunk_ev[16] = {};
     int host_chunks = 0;             // BS_HOST_CHUNKS (tuning), 0 = default
+    // split-phase host rollout (bs_rollout_fused_host_begin/_end): two action staging buffers (stage slots 8, 9)
+    // in rotation, so that the copies of call k+1 overlap the kernels of call k
+    cudaEvent_t call_done[2] = {};   // recorded on hstream after a call's last kernel and its counter read-back
+    cudaEvent_t copy_done = nullptr; // recorded on cstream after a call's last action copy
+    int64_t *pinned_stats = nullptr; // [2][8] pinned host memory
+    int inflight = 0, next_buf = 0;  // calls begun and not yet ended (0..2); staging buffer of the next call
     // device staging for *_host calls (grown on demand)
     void *stage[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t stage_sz[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -686,6 +727,7 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     if (!cfg || !out) return fail(BS_E_INVALID, "null argument");
     if (cfg->n_agents < 1 || cfg->n_agents > BS_MAX_AGENTS) return fail(BS_E_INVALID, "n_agents must be in 1..8");
     if (n_envs < 1 || env_offset < 0) return fail(BS_E_INVALID, "n_envs must be >= 1 and env_offset >= 0");
+    if (n_envs > (1ll << 30)) return fail(BS_E_INVALID, "n_envs must be <= 2^30 per handle (shard larger jobs by env_offset)");
     int ndev = 0;
     cudaError_t ce = cudaGetDeviceCount(&ndev);
     if (ce != cudaSuccess || ndev == 0)
@@ -705,6 +747,7 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     { const char *ex = getenv("BS_EXACT_TRIG"); p.exact_trig = ex && ex[0] == '1'; }
     p.r_hit_base = cfg->hit_base_reward; p.r_hit_plane = cfg->hit_plane_reward;
     p.r_miss = cfg->miss_punishment; p.r_die = cfg->die_punishment; p.r_lose = cfg->lose_punishment;
+    p.r_code[0] = 0.0; p.r_code[1] = p.r_miss; p.r_code[2] = p.r_hit_base; p.r_code[3] = p.r_hit_plane;
     p.diag = std::sqrt(std::pow(1200.0, 2) + std::pow(800.0, 2));
     if (p.diag != DIAG) { delete h; return fail(BS_E_INVALID, "host sqrt(1200^2+800^2) differs from the device constant"); }
     const size_t EP = (size_t)n_envs * h->P;
@@ -729,6 +772,9 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
     if (ce2 == cudaSuccess) ce2 = cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking);
     if (ce2 == cudaSuccess) ce2 = cudaStreamCreateWithFlags(&h->cstream, cudaStreamNonBlocking);
     for (auto &ev : h->chunk_ev) if (ce2 == cudaSuccess) ce2 = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    for (auto &ev : h->call_done) if (ce2 == cudaSuccess) ce2 = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (ce2 == cudaSuccess) ce2 = cudaEventCreateWithFlags(&h->copy_done, cudaEventDisableTiming);
+    if (ce2 == cudaSuccess) ce2 = cudaMallocHost(&h->pinned_stats, 16 * sizeof(int64_t));
     if (ce2 != cudaSuccess) {   // (a failure this late must not leak the handle and its allocations)
         bs_destroy(h);
         return fail(BS_E_CUDA, std::string("bs_create: ") + cudaGetErrorString(ce2));
@@ -747,6 +793,9 @@ int bs_destroy(bs_handle *h) {
     if (h->hstream) cudaStreamDestroy(h->hstream);
     if (h->cstream) cudaStreamDestroy(h->cstream);
     for (auto ev : h->chunk_ev) if (ev) cudaEventDestroy(ev);
+    for (auto ev : h->call_done) if (ev) cudaEventDestroy(ev);
+    if (h->copy_done) cudaEventDestroy(h->copy_done);
+    if (h->pinned_stats) cudaFreeHost(h->pinned_stats);
     delete h;
     return BS_OK;
 }
@@ -775,6 +824,7 @@ static int launch_step(bs_handle *h, const StepArgs &sa, cudaStream_t st) {
 static int replay_check(const bs_handle *h, const bs_replay *replay, int64_t T) {
     if (!replay || replay->capacity <= 0) return BS_OK;
     if (replay->capacity < h->E) return fail(BS_E_INVALID, "replay ring is smaller than n_envs: rows of different envs would collide");
+    if (replay->capacity > (int64_t)0x7fffffff / h->N) return fail(BS_E_INVALID, "replay ring too large: capacity * n_agents must stay below 2^31");
     if (T * h->E > replay->capacity && replay->capacity % h->E != 0)
         return fail(BS_E_INVALID, "a launch that wraps the replay ring (T * n_envs > capacity) needs capacity % n_envs == 0");
     return BS_OK;
@@ -1205,19 +1255,28 @@ int bs_instinct_actions_host(bs_handle *h, int team, const float *obs, const dou
 
 // The learner's actions arrive over PCIe (36 B per env-tick for 3v3), which takes longer than the
 // rollout itself.  The envs are therefore cut into chunks: chunk k+1's actions are copied (strided in
-// T, cudaMemcpy2DAsync on the copy stream) while chunk k's rollout runs on the compute stream.
-int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
-                          const float *ext_actions, const bs_replay *replay, int64_t cursor, int64_t stats_out[8]) {
+// T, cudaMemcpy2DAsync on the copy stream) while chunk k's rollout runs on the compute stream.  The call
+// is split in two phases so that a caller can also overlap ACROSS calls: _begin returns as soon as the host
+// action buffer has been consumed (its copies are done; the kernels may still be running), _end waits for
+// the oldest call in flight and hands back its counters.  Two staging buffers rotate, at most two calls are
+// in flight.  bs_rollout_fused_host = _begin + _end.
+int bs_rollout_fused_host_begin(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
+                                const float *ext_actions, const bs_replay *replay, int64_t cursor) {
     int rc = rollout_check(h, T, learner_team, policy_red, policy_blue, ext_actions, replay, cursor);  // (BS_POL_EXTERNAL without actions: BS_E_INVALID)
     if (rc) return rc;
+    if (h->inflight >= 2) return fail(BS_E_INVALID, "two host rollouts are already in flight: call bs_rollout_fused_host_end first");
     DeviceGuard guard(h->device);
+    const int buf = h->next_buf;
     if (!ext_actions) {
         rc = rollout_range(h, T, learner_team, policy_red, policy_blue, nullptr, replay, cursor, 0, h->E, h->hstream);
         if (rc) return rc;
     } else {
         const size_t row_bytes = (size_t)h->N * h->A * 4, pitch = (size_t)h->E * row_bytes;
         void *d_ext = nullptr;
-        rc = stage_buf(h, 8, (size_t)T * pitch, &d_ext); if (rc) return rc;
+        if (h->stage_sz[8 + buf] < (size_t)T * pitch) CU(cudaDeviceSynchronize());   // growing a staging buffer frees the old one
+        rc = stage_buf(h, 8 + buf, (size_t)T * pitch, &d_ext); if (rc) return rc;
+        // this staging buffer was last read by the call two calls ago: its kernels must have finished
+        CU(cudaStreamWaitEvent(h->cstream, h->call_done[buf], 0));
         const int K = 32 / h->P;
         int chunks = h->host_chunks > 0 ? h->host_chunks : 4;   // measured best of 3,4,6,8,12 at 65,536 envs (profiles/r1m_e2e_chunks.txt)
         int64_t per = (h->E + chunks - 1) / chunks;
@@ -1234,13 +1293,32 @@ int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red,
             rc = rollout_range(h, T, learner_team, policy_red, policy_blue, (const float *)d_ext, replay, cursor, e0, e1, h->hstream);
             if (rc) return rc;
         }
-        // the next call's first copy must not overtake this call's last kernel
-        CU(cudaEventRecord(h->chunk_ev[15], h->hstream));
-        CU(cudaStreamWaitEvent(h->cstream, h->chunk_ev[15], 0));
+        CU(cudaEventRecord(h->copy_done, h->cstream));
     }
-    if (stats_out) CU(cudaMemcpyAsync(stats_out, h->p.counters, 8 * sizeof(int64_t), cudaMemcpyDeviceToHost, h->hstream));
-    CU(cudaStreamSynchronize(h->hstream));
+    CU(cudaMemcpyAsync(h->pinned_stats + 8 * buf, h->p.counters, 8 * sizeof(int64_t), cudaMemcpyDeviceToHost, h->hstream));
+    CU(cudaEventRecord(h->call_done[buf], h->hstream));
+    h->inflight += 1; h->next_buf = 1 - buf;
+    if (ext_actions) CU(cudaEventSynchronize(h->copy_done));   // the caller may refill its action buffer now
     return BS_OK;
+}
+
+int bs_rollout_fused_host_end(bs_handle *h, int64_t stats_out[8]) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    if (h->inflight <= 0) return fail(BS_E_INVALID, "no host rollout in flight");
+    DeviceGuard guard(h->device);
+    const int buf = h->inflight == 2 ? h->next_buf : 1 - h->next_buf;   // the oldest call in flight
+    CU(cudaEventSynchronize(h->call_done[buf]));
+    if (stats_out) std::memcpy(stats_out, h->pinned_stats + 8 * buf, 8 * sizeof(int64_t));
+    h->inflight -= 1;
+    return BS_OK;
+}
+
+int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
+                          const float *ext_actions, const bs_replay *replay, int64_t cursor, int64_t stats_out[8]) {
+    if (h) while (h->inflight > 0) { int rc = bs_rollout_fused_host_end(h, nullptr); if (rc) return rc; }
+    int rc = bs_rollout_fused_host_begin(h, T, learner_team, policy_red, policy_blue, ext_actions, replay, cursor);
+    if (rc) return rc;
+    return bs_rollout_fused_host_end(h, stats_out);
 }
 
 }  // extern "C"

@@ -26,6 +26,16 @@ constexpr double RAD2DEG = 180.0 / PI;  // math.degrees
 constexpr double TWO_PI = 2 * PI;
 constexpr double DIAG = 1442.2205101855957;  // math.sqrt(1200**2 + 800**2), battle_env.py:230 (host asserts it)
 
+// The same doubles in constant memory.  A double literal whose low word is not zero cannot be an immediate
+// operand: the compiler materialises it with two UMOV per use -- 73 warp-instructions per tick (4.6 %) in r2a.
+// As constant-bank operands (`DADD R, R, c[3][..]`) they cost nothing.  (Not `const`: a const-initialised
+// __constant__ would be folded back into literals.)
+static __constant__ double KC_TWO_PI = TWO_PI, KC_PI = PI, KC_DEG2RAD = DEG2RAD, KC_RAD2DEG = RAD2DEG, KC_DIAG = DIAG,
+                           KC_RCP_DIAG = 1.0 / DIAG, KC_RCP_360 = 1.0 / 360.0, KC_RCP_35 = 1.0 / 35.0,
+                           KC_NOISE_LO = -0.15, KC_NOISE_W = 0.15 - -0.15,          // np.random.uniform(-0.15, 0.15): low + (high - low) * u
+                           KC_FIRE_P = 0.6, KC_FIRE_RANGE = 500.0 / 3 * 2,          // instinct/agent.py:43-44
+                           KC_TENTH = 0.1;
+
 // Bullet words.  pos: (x+64) | (y+64) << 16 | flags; the bias keeps both fields positive while a
 // bullet is one update past the field edge, so pos + dlt is ONE integer add (dlt = sx + sy*65536).
 constexpr uint32_t B_VALID = 1u << 31, B_XEXACT = 1u << 30, B_YEXACT = 1u << 29, B_POS = 0x1fffffffu;
@@ -47,6 +57,7 @@ struct Params {
     int tie_tick;         // first step call whose accumulated 0.1s reach 10+2N (battle_env.py:316-319)
     int exact_trig;       // BS_EXACT_TRIG=1 at bs_create: never speculate in fp32 (cos_sin_fast); for the parity test
     double r_hit_base, r_hit_plane, r_miss, r_die, r_lose;
+    double r_code[4];     // reward of a bullet event code: 0 none, 1 miss, 2 base hit, 3 plane hit (bullets_dense)
     double diag;          // == DIAG
     // SoA state (see DESIGN.md "Data layout in HBM")
     uint32_t *plane_pos;  // [E*2N]      x | y<<16
@@ -144,26 +155,42 @@ struct Geo {
     static constexpr int G = P;           // lanes per env
     static constexpr int K = 32 / G;      // envs per warp
     static constexpr int L = 3 * N + 2;   // observation length, battle_env.py:132
-    int lane, i, team, k;                 // lane in warp; agent index; team; index in team
-    int gb, tb, eb;                       // first lane of: my env, my team, the enemy team
-    bool valid;                           // lane maps to an env < E
-    long long e;                          // env index within the handle
+    // Lane constants, one byte each in two registers.  They are pure functions of threadIdx, which the compiler
+    // would rather recompute than keep when registers are short -- r1o/r2a spent 75 warp-instructions per tick
+    // (4.7 %) re-deriving them inside the tick loop.  The empty asm makes the packed words opaque, so a use
+    // costs one byte extract.
+    uint32_t pa;                          // lane | agent index i << 8 | index in team k << 16 | team << 24
+    uint32_t pb;                          // first lane of: my env (gb) | my team (tb) << 8 | the enemy team (eb) << 16 | valid << 24
+    int e32;                              // env index within the handle
 
     // the launch covers envs [e0, e_end) of the handle
     __device__ __forceinline__ Geo(long long warp_id, long long e_end, long long e0 = 0) {
-        lane = threadIdx.x & 31;
-        int sub = lane / G;
-        i = lane - sub * G;
-        team = i >= N;
-        k = i - team * N;
-        e = e0 + warp_id * K + sub;
-        valid = sub < K && e < e_end;
-        if (!valid) sub = 0;  // keep shuffle sources in range for idle lanes
-        gb = sub * G;
-        tb = gb + team * N;
-        eb = gb + (1 - team) * N;
+        const int lane_ = threadIdx.x & 31;
+        int sub = lane_ / G;
+        const int i_ = lane_ - sub * G;
+        const int team_ = i_ >= N;
+        const int k_ = i_ - team_ * N;
+        const long long e_ = e0 + warp_id * K + sub;
+        const bool valid_ = sub < K && e_ < e_end;
+        if (!valid_) sub = 0;  // keep shuffle sources in range for idle lanes
+        const int gb_ = sub * G;
+        pa = (uint32_t)lane_ | ((uint32_t)i_ << 8) | ((uint32_t)k_ << 16) | ((uint32_t)team_ << 24);
+        pb = (uint32_t)gb_ | ((uint32_t)(gb_ + team_ * N) << 8) | ((uint32_t)(gb_ + (1 - team_) * N) << 16) | ((valid_ ? 1u : 0u) << 24);
+        e32 = (int)e_;
+#ifndef BS_GEO_RECOMPUTE   // (A/B switch: without the barrier the compiler re-derives the fields where it uses them)
+        asm volatile("" : "+r"(pa), "+r"(pb), "+r"(e32));
+#endif
     }
-    __device__ __forceinline__ unsigned gmask() const { return (G == 32 ? FULL : ((1u << G) - 1u)) << gb; }
+    __device__ __forceinline__ int lane() const { return (int)__byte_perm(pa, 0, 0x4440); }
+    __device__ __forceinline__ int i() const { return (int)__byte_perm(pa, 0, 0x4441); }
+    __device__ __forceinline__ int k() const { return (int)__byte_perm(pa, 0, 0x4442); }
+    __device__ __forceinline__ int team() const { return (int)(pa >> 24); }
+    __device__ __forceinline__ int gb() const { return (int)__byte_perm(pb, 0, 0x4440); }
+    __device__ __forceinline__ int tb() const { return (int)__byte_perm(pb, 0, 0x4441); }
+    __device__ __forceinline__ int eb() const { return (int)__byte_perm(pb, 0, 0x4442); }
+    __device__ __forceinline__ bool valid() const { return (pb >> 24) != 0; }
+    __device__ __forceinline__ long long e() const { return (long long)e32; }
+    __device__ __forceinline__ unsigned gmask() const { return (G == 32 ? FULL : ((1u << G) - 1u)) << gb(); }
 };
 
 // Registers of one lane.
@@ -188,7 +215,7 @@ __device__ __forceinline__ void gather(const Geo<N> &g, Lane<N> &s) {
     s.am = 0; s.ehp4 = 0;
 #pragma unroll
     for (int j = 0; j < N; ++j) {
-        uint32_t v = __shfl_sync(FULL, mine, g.eb + j);
+        uint32_t v = __shfl_sync(FULL, mine, g.eb() + j);
         s.exy[j] = (v & 0x7ffu) | (((v >> 11) & 0x3ffu) << 16);
         uint32_t hp = (v >> 21) & 7u;
         s.ehp4 |= hp << (4 * j);
@@ -209,7 +236,7 @@ __device__ __forceinline__ double div_const(double a, double b, double rcp_b) {
 // float32(rel / 360) -- battle_env.py:231,242: the double quotient exactly as the reference rounds it, then
 // the float32 store.  (Until r1n this was rel * (1/360) with a guard that fell back to a real division
 // when the product sat within 4 ulps of a float rounding midpoint.)
-__device__ __forceinline__ float div360_f32(double rel) { return (float)div_const(rel, 360.0, 1.0 / 360.0); }
+__device__ __forceinline__ float div360_f32(double rel) { return (float)div_const(rel, 360.0, KC_RCP_360); }
 
 // rel_angle / 360 -- battle_env.py:38-52,231 ; dist / diag * 2 - 1 -- battle_env.py:54-58,230.
 // atan2, the % 2pi, degrees() and the sqrt were evaluated by the host for every integer (dx, dy);
@@ -235,14 +262,17 @@ __device__ __forceinline__ void pair_load(const Params &p, int dx, int dy, doubl
 // order, one rounding each: rads %= 2*pi (for a negative angle: + 2*pi), degrees(), 360 - degs, then
 // 180 + direction - that, wrapped into (-180, 180].
 __device__ __forceinline__ float pair_angle(double r0, bool neg, double a0) {
-    double r = neg ? -r0 : r0;
-    if (r < 0) r += TWO_PI;
-    const double t = 360 - r * RAD2DEG;
+    // atan2(dy, dx) = -r0 for dy < 0, and `rads %= 2*pi` then adds 2*pi: (-r0) + 2*pi == 2*pi - r0, one rounding
+    // either way (r0 > 0 whenever dy != 0, so the sign test of the reference is the sign of dy).
+    const double rn = KC_TWO_PI - r0;
+    const double r = neg ? rn : r0;
+    const double t = 360 - r * KC_RAD2DEG;
     double rel = 180 + a0 - t;
     // `if angle < -180: angle += 360` (battle_env.py:49) can never fire here: a plane's direction stays in
     // [0, 360] (Plane.rotate, sprites.py:100-103; bs_set_state rejects anything else), so 180 + a0 >= 180
-    // exactly, and t <= 360 exactly (r >= 0), hence rel >= -180.  Only the upper wrap is left.
-    if (rel > 180) rel -= 360;
+    // exactly, and t <= 360 exactly (r >= 0), hence rel >= -180.  Only the upper wrap is left; it subtracts
+    // 360.0 or 0.0 (only the high word differs: one select).
+    rel -= __hiloint2double(rel > 180 ? 0x40768000 : 0, 0);
     return div360_f32(rel);
 }
 
@@ -285,34 +315,46 @@ __device__ __forceinline__ void observe(const Params &p, const Lane<N> &s, float
     observe_finish<N>(s, q, o);
 }
 
+// min(max(v, -1), 1) for a finite v: one |v| > 1 test, then +-1 assembled from the sign bit (fmin/fmax on doubles
+// cost 13 instructions each with their NaN handling; two compare-selects cost 6-7).
+__device__ __forceinline__ double clamp1(double v) {
+    const bool big = fabs(v) > 1.0;
+    const int hi = __double2hiint(v), lo = __double2loint(v);
+    return __hiloint2double(big ? (int)(((uint32_t)hi & 0x80000000u) | 0x3ff00000u) : hi, big ? 0 : lo);
+}
+
+// 2 * (k / 2^24) - 1 for a 24-bit k, exactly: (2k - 2^24) is a 25-bit integer, its conversion and the scaling
+// by 2^-24 are exact, and so are the reference-order operations on k / 2^24 they replace.
+__device__ __forceinline__ double sym24(uint32_t k) { return __int2double_rn((int)(2u * k) - (1 << 24)) * (1.0 / 16777216.0); }
+
 // InstinctAgent.choose_action -- instinct/agent.py:10-62 (float32 obs decoded in double:
 // numpy 1.23.1 promotion).  Continuous: a[0..2]; discrete: adisc.
 template <int N, bool CONT>
 __device__ __forceinline__ void instinct(const float (&o)[3 * N + 2], double shoot_u,
                                          double n0, double n1, double n2, int &adisc, double (&a)[3]) {
-    double td = ((double)o[0] + 1) / 2 * DIAG;
+    double td = ((double)o[0] + 1) / 2 * KC_DIAG;
     double ta = (double)o[1] * 360;
     double best = td * fabs(ta);  // base wins ties: replaced only by a strictly smaller score
 #pragma unroll
     for (int j = 0; j < N; ++j) {
-        double dj = ((double)o[3 + 3 * j] + 1) / 2 * DIAG;
+        double dj = ((double)o[3 + 3 * j] + 1) / 2 * KC_DIAG;
         double aj = (double)o[4 + 3 * j] * 360;
         double sc = (o[2 + 3 * j] == 1.0f) ? dj * fabs(aj) : 1000000.0;
         if (sc < best) { best = sc; td = dj; ta = aj; }
     }
     if (CONT) {
         double a2 = 0;
-        if (td < 500.0 / 3 * 2 && fabs(ta) < 20) a2 = shoot_u < 0.6 ? 1.0 : -1.0;
-        double a0 = div_const(td, DIAG, 1.0 / DIAG) * 2 - 1;
+        if (td < KC_FIRE_RANGE && fabs(ta) < 20) a2 = shoot_u < KC_FIRE_P ? 1.0 : -1.0;
+        double a0 = div_const(td, KC_DIAG, KC_RCP_DIAG) * 2 - 1;
         // agent.py:47-50: max(v, -1) when ang > 0 (v < 0), min(v, 1) otherwise (v >= 0): one clamp covers both
-        // (no NaN can occur; fmax/fmin keep the sign of a zero like the reference's comparisons do)
-        const double v = div_const(-ta, 35.0, 1.0 / 35.0), a1 = fmin(fmax(v, -1.0), 1.0);
-        const double t0 = a0 + (-0.15 + (0.15 - -0.15) * n0);
-        const double t1 = a1 + (-0.15 + (0.15 - -0.15) * n1);
-        const double t2 = a2 + (-0.15 + (0.15 - -0.15) * n2);
-        a[0] = fmin(fmax(t0, -1.0), 1.0);   // np.clip, agent.py:54
-        a[1] = fmin(fmax(t1, -1.0), 1.0);
-        a[2] = fmin(fmax(t2, -1.0), 1.0);
+        // (no NaN can occur; clamp1 keeps the sign of a zero like the reference's comparisons do)
+        const double v = div_const(-ta, 35.0, KC_RCP_35), a1 = clamp1(v);
+        const double t0 = a0 + (KC_NOISE_LO + KC_NOISE_W * n0);
+        const double t1 = a1 + (KC_NOISE_LO + KC_NOISE_W * n1);
+        const double t2 = a2 + (KC_NOISE_LO + KC_NOISE_W * n2);
+        a[0] = clamp1(t0);   // np.clip, agent.py:54
+        a[1] = clamp1(t1);
+        a[2] = clamp1(t2);
         adisc = 0;
     } else {
         adisc = (td < 500.0 / 2 && fabs(ta) < 20) ? 1 : (ta > 0 ? 3 : 2);
@@ -322,7 +364,7 @@ __device__ __forceinline__ void instinct(const float (&o)[3 * N + 2], double sho
 
 // (cos, sin)(-radians(dir)) -- calc_new_xy, sprites.py:35-42.  Out of line: two call sites per tick.
 static __device__ __noinline__ double2 cos_sin_dir(double dir) {
-    double rad = -(dir * DEG2RAD);
+    double rad = -(dir * KC_DEG2RAD);
     double sn, cs;
     sincos(rad, &sn, &cs);
     return make_double2(cs, sn);
@@ -337,8 +379,8 @@ static __device__ __noinline__ double2 cos_sin_dir(double dir) {
 constexpr float FLOOR_GUARD = 2.5e-4f;
 
 __device__ __forceinline__ void cos_sin_fast(double dir, float &cs, float &sn) {
-    double rad = -(dir * DEG2RAD);       // dir in [-4, 364]: rad in [-6.36, 0.07]
-    if (rad < -PI) rad += TWO_PI;        // -> [-pi, pi]
+    double rad = -(dir * KC_DEG2RAD);    // dir in [-4, 364]: rad in [-6.36, 0.07]
+    if (rad < -KC_PI) rad += KC_TWO_PI;  // -> [-pi, pi]
     const float r = (float)rad;
     cs = __cosf(r); sn = __sinf(r);
 }
@@ -356,7 +398,7 @@ __device__ __forceinline__ bool floor_guarded(float v, int &fl) {
 // truncated or floored, so trunc(x + v) == x + floor(v) for the purpose of the clamped result.
 template <bool FAST>
 __device__ __forceinline__ void plane_forward(int &x, int &y, double dir, double speed, bool exact) {
-    const double st = speed * 0.1;
+    const double st = speed * KC_TENTH;
     int nx, ny;
     bool done = false;
     if (FAST && !exact) {
@@ -431,7 +473,7 @@ struct TickCtx {
 template <int N, bool CONT>
 __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lane<N> &s, int adisc,
                                            const double (&a)[3], double spread_u, bool no_actions, TickCtx &c) {
-    c.active = g.valid && !s.env_done;                                  // :303-306
+    c.active = g.valid() && !s.env_done;                                  // :303-306
     const unsigned alive_b = __ballot_sync(FULL, c.active && s.hp > 0);
     const bool any_alive = !no_actions && (alive_b & g.gmask()) != 0;   // len(actions) == 0 also ties
     c.tie_now = c.active && !any_alive;                                 // :309-313
@@ -518,14 +560,14 @@ __device__ __forceinline__ void resolve_plane_hits(const Geo<N> &g, Lane<N> &s, 
         for (int kk = 0; kk < N; ++kk) {
             const unsigned m = cm & s.am;
             const int c_me = m ? (__ffs(m) - 1) : -1;
-            const int c_team = __shfl_sync(FULL, c_me, g.tb + kk);   // teammate kk's victim
-            const int c_foe = __shfl_sync(FULL, c_me, g.eb + kk);    // enemy kk's victim
-            if (kk == g.k) victim = c_me;
+            const int c_team = __shfl_sync(FULL, c_me, g.tb() + kk);   // teammate kk's victim
+            const int c_foe = __shfl_sync(FULL, c_me, g.eb() + kk);    // enemy kk's victim
+            if (kk == g.k()) victim = c_me;
             if (c_team >= 0) {
                 s.ehp4 -= 1u << (4 * c_team);
                 if (((s.ehp4 >> (4 * c_team)) & 0xfu) == 0) s.am &= ~(1u << c_team);
             }
-            if (g.valid && c_foe == g.k && s.hp > 0) {
+            if (g.valid() && c_foe == g.k() && s.hp > 0) {
                 s.hp -= 1;
                 if (s.hp <= 0 && died_ai < 0) died_ai = ai;
             }
@@ -561,7 +603,7 @@ __host__ __device__ __forceinline__ int32_t meta_dlt(uint32_t m) { return (int32
 
 template <int N>
 __device__ __forceinline__ void pool_publish_base(const Geo<N> &g, const Lane<N> &s, WarpPool &w) {
-    w.baseT[g.lane] = ((((uint32_t)(s.ebx - 33)) | ((uint32_t)(s.eby - 32) << 16)) + B_BIAS) | ((uint32_t)g.eb << 27);
+    w.baseT[g.lane()] = ((((uint32_t)(s.ebx - 33)) | ((uint32_t)(s.eby - 32) << 16)) + B_BIAS) | ((uint32_t)g.eb() << 27);
 }
 
 // The bullets of an env that is reset vanish (self.bullets = [], battle_env.py:272): the callers drop them
@@ -569,7 +611,7 @@ __device__ __forceinline__ void pool_publish_base(const Geo<N> &g, const Lane<N>
 template <int N>
 __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpPool &w, int &cnt, const TickCtx &c,
                                               unsigned &ev, int &died_ai) {
-    const int lane = g.lane;
+    const int lane = g.lane();
     const unsigned lt = (1u << lane) - 1u;
     // a plane that is not in self.agents is published far off the field: every rect test against it fails
     w.plane[lane] = s.hp > 0 ? ((uint32_t)s.x | ((uint32_t)s.y << 16)) : 0x7fff7fffu;
@@ -698,16 +740,24 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
     rew = 0.0;
     // Rewards in the reference's accumulation order (:337-360): per age, own bullet outcome; a
     // victim's die_punishment precedes its own same-age outcome for blue (red bullets come first
-    // in the list) and follows it for red.
-    {
+    // in the list) and follows it for red.  A death is rare (once per plane and game), so the common
+    // loop only walks the lane's own events, oldest first; the rewards sit in a 4-entry table indexed
+    // by the event code.
+    if (!__any_sync(FULL, died_ai >= 0)) {
+        unsigned e2 = ev;
+        while (e2 != 0) {
+            const int sh = (__ffs(e2) - 1) & ~1;
+            rew += p.r_code[(e2 >> sh) & 3u];
+            e2 &= ~(3u << sh);
+        }
+    } else {
         unsigned e2 = ev;
         int da = died_ai;
         while (e2 != 0 || da >= 0) {
             const int ae = e2 ? ((__ffs(e2) - 1) >> 1) : 64;
-            if (da >= 0 && (da < ae || (da == ae && g.team == 1))) { rew += p.r_die; da = -1; }
+            if (da >= 0 && (da < ae || (da == ae && g.team() == 1))) { rew += p.r_die; da = -1; }
             else {
-                const unsigned code = (e2 >> (2 * ae)) & 3u;
-                rew += code == 1u ? p.r_miss : (code == 2u ? p.r_hit_base : p.r_hit_plane);
+                rew += p.r_code[(e2 >> (2 * ae)) & 3u];
                 e2 &= ~(3u << (2 * ae));
             }
         }
@@ -717,8 +767,8 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
     int mine_total = 0, foe_total = 0;
 #pragma unroll
     for (int kk = 0; kk < N; ++kk) {
-        mine_total += __shfl_sync(FULL, base_hits, g.tb + kk);
-        foe_total += __shfl_sync(FULL, base_hits, g.eb + kk);
+        mine_total += __shfl_sync(FULL, base_hits, g.tb() + kk);
+        foe_total += __shfl_sync(FULL, base_hits, g.eb() + kk);
     }
     s.bhp_enemy -= mine_total;
     s.bhp_own -= foe_total;
@@ -727,7 +777,7 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
     const bool i_won = c.run && s.bhp_enemy <= 0;  // the winners' planes get lose_punishment (sic)
     const bool foe_won = c.run && s.bhp_own <= 0;
     if (i_won) rew += p.r_lose;
-    const bool red_won = g.team == 0 ? i_won : foe_won, blue_won = g.team == 0 ? foe_won : i_won;
+    const bool red_won = g.team() == 0 ? i_won : foe_won, blue_won = g.team() == 0 ? foe_won : i_won;
     const bool tie = c.tie_now || c.time_tie;
     if (red_won) s.winner = W_RED;
     if (blue_won) s.winner = W_BLUE;  // both bases dead: ends as 'blue', two games counted
@@ -738,10 +788,10 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
     double r0 = 0, r1 = 0;
 #pragma unroll
     for (int kk = 0; kk < N; ++kk) {
-        r0 += __shfl_sync(FULL, rew, g.gb + kk);
-        r1 += __shfl_sync(FULL, rew, g.gb + N + kk);
+        r0 += __shfl_sync(FULL, rew, g.gb() + kk);
+        r1 += __shfl_sync(FULL, rew, g.gb() + N + kk);
     }
-    const bool first = c.active && g.i == 0;
+    const bool first = c.active && g.i() == 0;
     if (first) { ret0 += r0; ret1 += r1; tl.ticks += 1; }
     const bool ended = first && s.env_done;
     if (__any_sync(FULL, ended)) {
@@ -756,7 +806,7 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
             p.ep_log[slot * 3 + 2] = tie ? 3.0f : (red_won && blue_won ? 6.0f : (red_won ? 1.0f : 2.0f));
         }
 #endif
-        if (g.lane == 0) {
+        if (g.lane() == 0) {
             if (nr) atomicAdd(p.counters + C_WINS_RED, (unsigned long long)nr);
             if (nb) atomicAdd(p.counters + C_WINS_BLUE, (unsigned long long)nb);
             if (nt) atomicAdd(p.counters + C_TIES, (unsigned long long)nt);
@@ -776,20 +826,20 @@ __device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lan
     int rbx, rby, bbx, bby, px, py, pd;
     if (inj) {
         rbx = draws[0]; rby = draws[1]; bbx = draws[2]; bby = draws[3];
-        px = draws[4 + 3 * g.i]; py = draws[5 + 3 * g.i]; pd = draws[6 + 3 * g.i];
+        px = draws[4 + 3 * g.i()]; py = draws[5 + 3 * g.i()]; pd = draws[6 + 3 * g.i()];
     } else {
         uint32_t w[4];
-        env_philox(p, g.e, s.episode, 0, 0, PURPOSE_RESET_BASE, w);
+        env_philox(p, g.e(), s.episode, 0, 0, PURPOSE_RESET_BASE, w);
         rbx = randint_from(w[0], 62, 379); rby = randint_from(w[1], 62, 738);       // sprites.py:246-247
         bbx = randint_from(w[2], 758, 1138); bby = randint_from(w[3], 62, 738);     // sprites.py:250-251
-        env_philox(p, g.e, s.episode, 0, g.i, PURPOSE_RESET_PLANE, w);
-        if (g.team == 0) { px = randint_from(w[0], 50, 383); pd = randint_from(w[2], 270, 450); }  // :82-85
+        env_philox(p, g.e(), s.episode, 0, g.i(), PURPOSE_RESET_PLANE, w);
+        if (g.team() == 0) { px = randint_from(w[0], 50, 383); pd = randint_from(w[2], 270, 450); }  // :82-85
         else { px = randint_from(w[0], 766, 1150); pd = randint_from(w[2], 90, 270); }             // :88-91
         py = randint_from(w[1], 48, 752);
     }
-    if (g.team == 0 && pd >= 360) pd -= 360;                                        // sprites.py:86
+    if (g.team() == 0 && pd >= 360) pd -= 360;                                        // sprites.py:86
     s.x = px; s.y = py; s.dir = (double)pd; s.hp = 4;                               // battle_env.py:92
-    s.ebx = g.team == 0 ? bbx : rbx; s.eby = g.team == 0 ? bby : rby;
+    s.ebx = g.team() == 0 ? bbx : rbx; s.eby = g.team() == 0 ? bby : rby;
     s.bhp_own = s.bhp_enemy = 5 * N;                                                // battle_env.py:91
     s.tick = 0; s.env_done = 0; s.winner = W_NONE;   // (the caller drops the env's bullets: kill / pool_filter)
 }
@@ -800,20 +850,20 @@ __device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane
     constexpr int P = 2 * N;
     s.x = s.y = 0; s.hp = 0; s.dir = 0; s.ebx = s.eby = 64; s.bhp_own = s.bhp_enemy = 0;
     s.tick = 0; s.env_done = 1; s.winner = 0; s.episode = 0; ret0 = ret1 = 0;
-    if (g.valid) {
-        const long long a = g.e * P + g.i;
+    if (g.valid()) {
+        const long long a = g.e() * P + g.i();
         uint32_t pos = p.plane_pos[a];
         s.x = pos & 0xffff; s.y = pos >> 16;
         s.dir = p.plane_dir[a];
         s.hp = p.plane_hp[a];
-        uint32_t eb = p.base_pos[g.e * 2 + (1 - g.team)];
+        uint32_t eb = p.base_pos[g.e() * 2 + (1 - g.team())];
         s.ebx = eb & 0xffff; s.eby = eb >> 16;
-        s.bhp_own = p.base_hp[g.e * 2 + g.team];
-        s.bhp_enemy = p.base_hp[g.e * 2 + (1 - g.team)];
-        uint32_t m = p.meta[g.e];
+        s.bhp_own = p.base_hp[g.e() * 2 + g.team()];
+        s.bhp_enemy = p.base_hp[g.e() * 2 + (1 - g.team())];
+        uint32_t m = p.meta[g.e()];
         s.tick = m & 0xfff; s.env_done = (m >> 16) & 0xff; s.winner = (m >> 24) & 0xff;
-        s.episode = p.episode[g.e];
-        if (g.i == 0) { ret0 = p.ret[g.e * 2]; ret1 = p.ret[g.e * 2 + 1]; }
+        s.episode = p.episode[g.e()];
+        if (g.i() == 0) { ret0 = p.ret[g.e() * 2]; ret1 = p.ret[g.e() * 2 + 1]; }
     }
 }
 
@@ -821,19 +871,19 @@ template <int N>
 __device__ __forceinline__ void store_lane(const Params &p, const Geo<N> &g, const Lane<N> &s, double ret0, double ret1,
                                            bool base_pos_too) {
     constexpr int P = 2 * N;
-    if (!g.valid) return;
-    const long long a = g.e * P + g.i;
+    if (!g.valid()) return;
+    const long long a = g.e() * P + g.i();
     p.plane_pos[a] = (uint32_t)s.x | ((uint32_t)s.y << 16);
     p.plane_dir[a] = s.dir;
     p.plane_hp[a] = (int8_t)s.hp;
-    if (g.k == 0) {  // first lane of each team owns its enemy's base record
-        p.base_hp[g.e * 2 + (1 - g.team)] = (int16_t)s.bhp_enemy;
-        if (base_pos_too) p.base_pos[g.e * 2 + (1 - g.team)] = (uint32_t)s.ebx | ((uint32_t)s.eby << 16);
+    if (g.k() == 0) {  // first lane of each team owns its enemy's base record
+        p.base_hp[g.e() * 2 + (1 - g.team())] = (int16_t)s.bhp_enemy;
+        if (base_pos_too) p.base_pos[g.e() * 2 + (1 - g.team())] = (uint32_t)s.ebx | ((uint32_t)s.eby << 16);
     }
-    if (g.i == 0) {
-        p.meta[g.e] = (uint32_t)s.tick | ((uint32_t)s.env_done << 16) | ((uint32_t)s.winner << 24);
-        p.episode[g.e] = s.episode;
-        p.ret[g.e * 2] = ret0; p.ret[g.e * 2 + 1] = ret1;
+    if (g.i() == 0) {
+        p.meta[g.e()] = (uint32_t)s.tick | ((uint32_t)s.env_done << 16) | ((uint32_t)s.winner << 24);
+        p.episode[g.e()] = s.episode;
+        p.ret[g.e() * 2] = ret0; p.ret[g.e() * 2 + 1] = ret1;
     }
 }
 

@@ -18,6 +18,7 @@
  *   bs_step_team_replay  the same + ReplayBuffer.store_transition   main.py:205, maddpg/buffer.py:25-47
  *   bs_rollout_fused     the whole inner game loop incl. ReplayBuffer.store_transition
  *                                                         main.py:178-213, maddpg/buffer.py:25-47
+ *   bs_rollout_fused_host[_begin/_end]   the same with the learner's actions in HOST memory
  *   bs_actor_forward     NetworkedAgent.choose_action for a whole team (row f1)
  *                                                         maddpg/networks.py:54-85, maddpg/agent.py:25-33,
  *                                                         utils/noise.py:17-21, maddpg/team.py:21-28
@@ -278,6 +279,14 @@ int bs_instinct_actions_host(bs_handle *h, int team, const float *obs, const dou
 int bs_rollout_fused_host(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
                           const float *ext_actions, const bs_replay *replay, int64_t cursor,
                           int64_t stats_out[8]);
+/* The same call in two phases, for a caller that prepares the next action block while the device works
+ * (main.py:178-213 with the actors on the host): _begin returns once ext_actions has been copied (the host
+ * buffer may be refilled; the kernels may still run), _end waits for the OLDEST call in flight and returns the
+ * counters as they stood after it.  At most two calls may be in flight (BS_E_INVALID otherwise); the action
+ * copies of call k+1 then overlap the kernels of call k. */
+int bs_rollout_fused_host_begin(bs_handle *h, int T, int learner_team, int policy_red, int policy_blue,
+                                const float *ext_actions, const bs_replay *replay, int64_t cursor);
+int bs_rollout_fused_host_end(bs_handle *h, int64_t stats_out[8]);
 
 #ifdef __cplusplus
 }

@@ -52,3 +52,30 @@ if "--sass" in sys.argv:
         if lo <= key[1] <= hi and (f is None or key[0].startswith(f)):
             s, i, t, sm = addr_info[a]
             print(f"{key[0][:10]}:{key[1]:4d} {i/W:5.2f} thr {t/i if i else 0:4.1f} smp {sm:5.0f}  {s}")
+if "--funcs" in sys.argv:
+    # enclosing function of a source line: the nearest non-indented line above it that opens a body
+    import os
+    srcdir = sys.argv[sys.argv.index("--funcs") + 1]
+    fmap = {}
+    def enclosing(fn, ln):
+        if fn not in fmap:
+            path = os.path.join(srcdir, fn)
+            heads = []
+            if os.path.exists(path):
+                for i, l in enumerate(open(path), 1):
+                    if l[:1] not in (" ", "\t", "#", "/", "}", "\n") and "(" in l:
+                        m = re.search(r"([A-Za-z_][A-Za-z0-9_]*)\s*\(", l.split("(")[0] + "(")
+                        heads.append((i, m.group(1) if m else l.strip()[:30]))
+            fmap[fn] = heads
+        name = fn
+        for i, h in fmap[fn]:
+            if i <= ln: name = h
+            else: break
+        return name
+    bf = collections.defaultdict(lambda: [0, 0, 0])
+    for key, b in bl.items():
+        f = enclosing(key[0], key[1]) if key else "?"
+        bf[f][0] += b[0]; bf[f][1] += b[1]; bf[f][2] += b[2]
+    for f, b in sorted(bf.items(), key=lambda kv: -kv[1][0]):
+        if b[0] == 0: continue
+        print(f"{f[:28]:28s} {b[0]/W:7.1f}/wt {100*b[0]/tot:5.1f}%  samp {100*b[2]/tots:5.1f}%  thr {b[1]/b[0]:4.1f}")

@@ -242,6 +242,47 @@ def test_rollout_host_pipelined_equals_device(N, cont, E, cuda_device):
 
 
 @pytest.mark.gpu
+def test_rollout_host_split_phase_two_calls_in_flight(cuda_device):
+    """bs_rollout_fused_host_begin/_end with two calls in flight (the copies of call k+1 overlap the kernels of
+    call k, two staging buffers rotate): the host buffer is refilled right after _begin returns; counters per call,
+    rows and state must equal the synchronous device path."""
+    import torch
+    from battlespace import DeviceReplay, _lib
+    from battlespace._lib import lib
+    from cuda_adapter import CudaEnv
+    N, cont, E, T, calls = 3, True, 24000, 8, 5
+    L, A = 3 * N + 2, 3
+    a = CudaEnv(N, cont, TRAINED_REWARDS, E, seed=6)
+    b = CudaEnv(N, cont, TRAINED_REWARDS, E, seed=6)
+    ra, rb = DeviceReplay(3 * T * E, 512, N, L, A, a.dev), DeviceReplay(3 * T * E, 512, N, L, A, b.dev)
+    rng = np.random.RandomState(12)
+    blocks = [rng.uniform(-1.2, 1.2, (T, E, N, A)).astype(np.float32) for _ in range(calls)]
+    want = []
+    for blk in blocks:
+        a.env.rollout(T, "external", "instinct", 0, torch.from_numpy(blk).to(a.dev), ra)
+        want.append(a.stats())
+    host = torch.empty((T, E, N, A), dtype=torch.float32).pin_memory()
+    got = []
+    host.copy_(torch.from_numpy(blocks[0]))
+    b.env.rollout_host_begin(T, "external", "instinct", 0, host, rb)
+    for k in range(1, calls):
+        host.copy_(torch.from_numpy(blocks[k]))              # overwritten while call k-1 may still be running
+        b.env.rollout_host_begin(T, "external", "instinct", 0, host, rb)
+        got.append(b.env.rollout_host_end())
+    assert lib.bs_rollout_fused_host_begin(b.env._h, T, 0, _lib.POL_RANDOM, _lib.POL_INSTINCT, None, None, 0) == 0
+    assert lib.bs_rollout_fused_host_begin(b.env._h, T, 0, _lib.POL_RANDOM, _lib.POL_INSTINCT, None, None, 0) == _lib.BS_E_INVALID
+    got.append(b.env.rollout_host_end())
+    assert lib.bs_rollout_fused_host_end(b.env._h, None) == 0 and lib.bs_rollout_fused_host_end(b.env._h, None) == _lib.BS_E_INVALID
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    a.env.rollout(T, "random", "instinct")                   # the extra in-kernel call above
+    _state_equal(a.get_state(), b.get_state())
+    for x, y in ((ra.state_mem, rb.state_mem), (ra.new_state_mem, rb.new_state_mem), (ra.action_mem, rb.action_mem),
+                 (ra.rew_mem, rb.rew_mem), (ra.done_mem, rb.done_mem)):
+        assert torch.equal(x, y)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("N,cont,E,ticks,auto", [(3, True, 3000, 208, False), (2, False, 2000, 176, False),
                                                  (3, True, 3000, 208, True), (1, False, 4000, 144, True)])
 def test_step_team_replay_equals_fused_rollout(N, cont, E, ticks, auto, cuda_device):
