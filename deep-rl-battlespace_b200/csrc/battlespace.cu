@@ -8,6 +8,7 @@
 // There is no CPU path in this library.
 #include "../../include/battlespace.h"
 #include "tick.cuh"
+#include "rollout2.cuh"
 #include "actor.cuh"
 #include "render.cuh"
 
@@ -331,16 +332,6 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     flush_tally<N>(p, tl);
 }
 
-struct RolloutArgs {
-    int T, learner;
-    int pol[2];
-    const float *ext;     // [T,E,N,A] learner actions when pol[learner] == POL_EXTERNAL
-    bs_replay rp;
-    long long cursor_mod; // cursor % capacity
-    long long e_mod;      // E % capacity
-    long long e0, e_end;  // env range of this launch (the host entry point pipelines chunks)
-};
-
 // 128-thread blocks x 8 resident (32 warps per SM at 64 registers); 6, 7, 9 and 10 resident blocks measured slower (r1).
 #ifndef ROLLOUT_BLOCK
 #define ROLLOUT_BLOCK 128
@@ -543,6 +534,11 @@ struct bs_handle {
     Params p;
     ObsTables tables;
     std::vector<void *> allocs;
+    // Bullets live in one of two HBM layouts: the per-warp pools of the lane-per-plane kernels (reset, step, render,
+    // state export) or the per-team lists of rollout2_kernel; ensure_bullets() converts when a call needs the other one.
+    int bullet_fmt = 0;              // FMT_POOLS / FMT_LISTS
+    bool rollout_v2 = false;         // BS_ROLLOUT_V2=1 at bs_create: the fused rollout runs the team-per-thread kernel (rollout2.cuh;
+                                     // measured slower than the lane-per-plane kernel at 3v3, DESIGN.md 7: kept for A/B and as a cross-check)
     cudaStream_t hstream = nullptr;  // used by the *_host entry points
     cudaStream_t cstream = nullptr;  // copy stream of bs_rollout_fused_host
     cudaEvent_t chunk_ev[16] = {};
@@ -642,13 +638,14 @@ static int tie_tick_for(int n_agents) {  // battle_env.py:316-319: total_time ac
 }
 
 static thread_local bool g_pdl = false;  // set by bs_rollout_actor around its launch loop
+static thread_local size_t g_dyn_smem = 0;  // unused dynamic shared memory of the next launch: caps the resident blocks per SM (rollout_range)
 
 // Kernel launch with the observation tables marked persisting in L2 for this launch only (the
 // caller's stream is not modified).
 template <class... KArgs, class... Args>
 static cudaError_t launch(const bs_handle *h, void (*kern)(KArgs...), int grid, int block, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = g_dyn_smem; cfg.stream = st;
     cudaLaunchAttribute attr[2];
     if (g_pdl) {  // programmatic dependent launch: this kernel may start while its predecessor drains (bs_rollout_actor)
         attr[cfg.numAttrs].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -668,6 +665,8 @@ static cudaError_t launch(const bs_handle *h, void (*kern)(KArgs...), int grid, 
     return cudaLaunchKernelEx(&cfg, kern, args...);
 }
 
+enum { FMT_POOLS = 0, FMT_LISTS = 1 };
+
 static inline int grid_for_envs(int64_t E, int N, int block = BLOCK) {
     const int K = 32 / (2 * N);
     const int64_t warps = (E + K - 1) / K;
@@ -686,6 +685,45 @@ static inline int grid_for_envs(int64_t E, int N, int block = BLOCK) {
         case 8: { constexpr int N_ = 8; __VA_ARGS__; } break;                \
         default: return fail(BS_E_INVALID, "n_agents out of range");         \
     }
+
+// rollout2_kernel keeps both teams' observation rows of 32 envs in static shared memory: 29 KB at N = 5, over the
+// 48 KB static limit from N = 7; team sizes above 5 (none of the BASELINE configs) stay on the lane-per-plane kernel.
+#ifdef R2_SMEM_BULLETS   // (A/B build: the lists in shared memory instead of local memory; fits up to N = 3)
+constexpr int R2_MAX_N = 3;
+#define DISPATCH_R2(n_, ...)                                                 \
+    switch (n_) {                                                            \
+        case 1: { constexpr int N_ = 1; __VA_ARGS__; } break;                \
+        case 2: { constexpr int N_ = 2; __VA_ARGS__; } break;                \
+        case 3: { constexpr int N_ = 3; __VA_ARGS__; } break;                \
+        default: return fail(BS_E_INVALID, "n_agents out of range");         \
+    }
+#else
+constexpr int R2_MAX_N = 5;
+#define DISPATCH_R2(n_, ...)                                                 \
+    switch (n_) {                                                            \
+        case 1: { constexpr int N_ = 1; __VA_ARGS__; } break;                \
+        case 2: { constexpr int N_ = 2; __VA_ARGS__; } break;                \
+        case 3: { constexpr int N_ = 3; __VA_ARGS__; } break;                \
+        case 4: { constexpr int N_ = 4; __VA_ARGS__; } break;                \
+        case 5: { constexpr int N_ = 5; __VA_ARGS__; } break;                \
+        default: return fail(BS_E_INVALID, "n_agents out of range");         \
+    }
+#endif
+
+// Converts the bullets to the layout the next kernel reads (a no-op when it is current); see rollout2.cuh.
+static int ensure_bullets(bs_handle *h, int fmt, cudaStream_t st) {
+    if (h->bullet_fmt == fmt) return BS_OK;
+    if (fmt == FMT_LISTS) {
+        const int grid = (int)((h->E + 31) / 32);
+        DISPATCH_N(h->N, pools_to_lists_kernel<N_><<<grid, 64, 0, st>>>(h->p));
+    } else {
+        const int grid = (int)((h->W * 32 + 127) / 128);
+        DISPATCH_N(h->N, lists_to_pools_kernel<N_><<<grid, 128, 0, st>>>(h->p));
+    }
+    CU(cudaGetLastError());
+    h->bullet_fmt = fmt;
+    return BS_OK;
+}
 
 // ---- actors (row f1) -------------------------------------------------------------------------------
 static int launch_actor(bs_handle *h, const ActorArgs &aa, cudaStream_t st) {
@@ -758,7 +796,9 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
         (rc = dalloc(h, &p.base_pos, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.base_hp, (size_t)n_envs * 2)) ||
         (rc = dalloc(h, &p.pool, (size_t)h->W * POOL_CAP)) || (rc = dalloc(h, &p.pool_cnt, (size_t)h->W)) ||
         (rc = dalloc(h, &p.meta, (size_t)n_envs)) || (rc = dalloc(h, &p.episode, (size_t)n_envs)) ||
-        (rc = dalloc(h, &p.ret, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.counters, 9))) {
+        (rc = dalloc(h, &p.ret, (size_t)n_envs * 2)) || (rc = dalloc(h, &p.counters, 9)) ||
+        (rc = dalloc(h, &p.lists, (size_t)((n_envs + 31) / 32) * SLOTS * h->N * 64)) ||
+        (rc = dalloc(h, &p.list_cnt, (size_t)((n_envs + 31) / 32) * 64))) {
         bs_destroy(h);
         return rc;
     }
@@ -779,6 +819,7 @@ int bs_create(const bs_config *cfg, int64_t n_envs, int64_t env_offset, int devi
         bs_destroy(h);
         return fail(BS_E_CUDA, std::string("bs_create: ") + cudaGetErrorString(ce2));
     }
+    { const char *v2 = getenv("BS_ROLLOUT_V2"); h->rollout_v2 = v2 && v2[0] == '1'; }
     if (const char *hc = getenv("BS_HOST_CHUNKS")) h->host_chunks = atoi(hc) > 15 ? 15 : atoi(hc);
     *out = h;
     return BS_OK;
@@ -804,6 +845,7 @@ int bs_reset(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float 
     if (!h) return fail(BS_E_INVALID, "null handle");
     DeviceGuard guard(h->device);
     cudaStream_t st = (cudaStream_t)stream;
+    { int rc = ensure_bullets(h, FMT_POOLS, st); if (rc) return rc; }
     const int grid = grid_for_envs(h->E, h->N);
     DISPATCH_N(h->N, reset_kernel<N_><<<grid, BLOCK, 0, st>>>(h->p, env_mask, draws, obs));
     CU(cudaGetLastError());
@@ -811,6 +853,7 @@ int bs_reset(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float 
 }
 
 static int launch_step(bs_handle *h, const StepArgs &sa, cudaStream_t st) {
+    { int rc = ensure_bullets(h, FMT_POOLS, st); if (rc) return rc; }
     const int grid = grid_for_envs(h->E, h->N, STEP_BLOCK);
     if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true>, grid, STEP_BLOCK, st, h->p, sa))); }
     else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false>, grid, STEP_BLOCK, st, h->p, sa))); }
@@ -913,7 +956,17 @@ static int rollout_range(bs_handle *h, int T, int learner_team, int policy_red, 
     } else {
         std::memset(&ra.rp, 0, sizeof(ra.rp));
     }
+    if (h->rollout_v2 && h->N <= R2_MAX_N) {   // team-per-thread mapping (rollout2.cuh): blocks of 32 envs, chunks start on a block boundary
+        if (e0 % 32 != 0) return fail(BS_E_INVALID, "rollout chunk does not start on a 32-env boundary");
+        int rc = ensure_bullets(h, FMT_LISTS, st); if (rc) return rc;
+        const int grid = (int)((e_end - e0 + 31) / 32);
+        if (h->cont) { DISPATCH_R2(h->N, CU(launch(h, rollout2_kernel<N_, true>, grid, 64, st, h->p, ra))); }
+        else { DISPATCH_R2(h->N, CU(launch(h, rollout2_kernel<N_, false>, grid, 64, st, h->p, ra))); }
+        return BS_OK;
+    }
+    { int rc = ensure_bullets(h, FMT_POOLS, st); if (rc) return rc; }
     const int grid = grid_for_envs(e_end - e0, h->N, ROLLOUT_BLOCK);
+    struct DynScope { DynScope() { const char *v = getenv("BS_ROLLOUT_DYNSMEM"); g_dyn_smem = v ? (size_t)atoi(v) : 0; } ~DynScope() { g_dyn_smem = 0; } } dyn_scope;
     if (h->cont) { DISPATCH_N(h->N, CU(launch(h, rollout_kernel<N_, true>, grid, ROLLOUT_BLOCK, st, h->p, ra))); }
     else { DISPATCH_N(h->N, CU(launch(h, rollout_kernel<N_, false>, grid, ROLLOUT_BLOCK, st, h->p, ra))); }
     return BS_OK;
@@ -992,6 +1045,7 @@ int bs_render(bs_handle *h, int64_t env, const bs_sprites *sprites, uint8_t *rgb
     if (sprites->n_explosions < 0) return fail(BS_E_INVALID, "n_explosions must be >= 0");
     RenderArgs ra{env, {sprites->plane[0], sprites->plane[1]}, {sprites->base[0], sprites->base[1]}, rgb,
                   sprites->explosion_img, sprites->explosions, sprites->n_explosions};
+    { int rc = ensure_bullets(h, FMT_POOLS, (cudaStream_t)stream); if (rc) return rc; }
     const int grid = (R_W * R_H + 255) / 256;
     DISPATCH_N(h->N, render_kernel<N_><<<grid, 256, 0, (cudaStream_t)stream>>>(h->p, ra));
     CU(cudaGetLastError());
@@ -1033,6 +1087,8 @@ int bs_stats_device(bs_handle *h, int64_t **dev_counters) {
 int bs_get_state(bs_handle *h, const bs_state_view *v) {
     if (!h || !v) return fail(BS_E_INVALID, "null argument");
     DeviceGuard guard(h->device);
+    CU(cudaDeviceSynchronize());
+    { int rc = ensure_bullets(h, FMT_POOLS, nullptr); if (rc) return rc; }
     CU(cudaDeviceSynchronize());
     const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
     std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), epi((size_t)E);
@@ -1151,6 +1207,7 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     CU(cudaMemcpy(p.base_hp, v->base_hp, (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.pool, pool.data(), pool.size() * sizeof(uint2), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.pool_cnt, pcnt.data(), pcnt.size() * sizeof(int), cudaMemcpyHostToDevice));
+    h->bullet_fmt = FMT_POOLS;
     CU(cudaMemcpy(p.meta, meta.data(), (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.episode, v->episode, (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.ret, v->team_return, (size_t)E * 16, cudaMemcpyHostToDevice));
@@ -1280,7 +1337,7 @@ int bs_rollout_fused_host_begin(bs_handle *h, int T, int learner_team, int polic
         const int K = 32 / h->P;
         int chunks = h->host_chunks > 0 ? h->host_chunks : 4;   // measured best of 3,4,6,8,12 at 65,536 envs (profiles/r1m_e2e_chunks.txt)
         int64_t per = (h->E + chunks - 1) / chunks;
-        per = (per + K - 1) / K * K;                       // whole warps per chunk
+        per = (per + 32 * K - 1) / (32 * K) * (32 * K);    // whole warps (lane-per-plane) and whole 32-env blocks (team-per-thread) per chunk
         if (per < 4096) per = h->E;                        // small handles: one chunk
         int k = 0;
         for (int64_t e0 = 0; e0 < h->E; e0 += per, ++k) {

@@ -67,6 +67,8 @@ struct Params {
     int16_t *base_hp;     // [E*2]
     uint2 *pool;          // [W][POOL_CAP] W = ceil(E/K) warps: the warp's bullets, packed (x = pos word, y = meta word)
     int *pool_cnt;        // [W]         entries in use (dead entries are squeezed out by the next pass)
+    uint2 *lists;         // [ceil(E/32)][12N][64]  the same bullets as per-team lists, rollout2.cuh (one of the two layouts is current)
+    int *list_cnt;        // [ceil(E/32)][64]
     uint32_t *meta;       // [E]         tick | env_done<<16 | winner<<24
     uint32_t *episode;    // [E]
     double *ret;          // [E*2]
@@ -469,7 +471,58 @@ struct TickCtx {
     int32_t spawnD;    // sx + sy * 65536
 };
 
-//   adisc / a[3] : this lane's decoded action (clipped / argmax-ed);  spread_u : its Bullet draw.
+// process_action of ONE plane -- battle_env.py:383-424 -- and the bullet it may spawn (Bullet.__init__,
+// sprites.py:293-318).  acts: the plane is alive and its env runs this tick.  Shared by the lane-per-plane
+// kernels (tick_begin) and the team-per-thread rollout (rollout2.cuh).
+//   adisc / a[3] : the decoded action (clipped / argmax-ed);  spread_u : its Bullet draw.
+//   spawnP / spawnD : bullet pos word (0 = no spawn) and sx + sy * 65536.
+template <bool CONT>
+__device__ __forceinline__ void plane_action(const Params &p, int &x, int &y, double &dir, bool acts, int adisc,
+                                             const double (&a)[3], double spread_u, uint32_t &spawnP, int32_t &spawnD) {
+    const int x0 = x, y0 = y;
+    const double d0 = dir;
+    bool shoot = false;
+    if (acts) {
+        double mdir = dir, speed = 215;
+        bool move = true;
+        if (CONT) {
+            speed = ((a[0] + 1) / 2) * (275 - 200) + 200;
+        } else {
+            move = adisc >= 0 && adisc <= 3;
+            shoot = adisc == 1;
+            if (adisc == 2) mdir = plane_rotate(dir, 15);
+            if (adisc == 3) mdir = plane_rotate(dir, -15);
+        }
+        if (move) plane_forward<CONT>(x, y, mdir, speed, p.exact_trig != 0);
+        if (CONT) { dir = plane_rotate(dir, a[1] * 35); shoot = a[2] > 0; }
+        else dir = mdir;
+    }
+    // Bullet.__init__ -- sprites.py:293-318.  From here on the bullet is integer: its per-update
+    // displacement d = 45*cos/sin is constant, and trunc(int + d) == int + floor(d) except that
+    // a result in (-1,0) truncates to 0 (flagged "exact" when d itself is an integer).
+    spawnP = 0; spawnD = 0;
+    if (shoot) {
+        const double bdir = d0 + (spread_u * 8 - 4);
+        const uint32_t at = (((uint32_t)x0 | ((uint32_t)y0 << 16)) + B_BIAS) | B_VALID;
+        bool done = false;
+        if (CONT && !p.exact_trig) {  // fp32 speculation, see cos_sin_fast: a guarded floor is never an exact integer
+            float cs, sn;
+            cos_sin_fast(bdir, cs, sn);
+            int fx, fy;
+            const bool okx = floor_guarded(45.0f * cs, fx), oky = floor_guarded(45.0f * sn, fy);
+            done = okx && oky;
+            spawnP = at; spawnD = fx + fy * 65536;
+        }
+        if (!done) {
+            double2 cssn = cos_sin_dir(bdir);
+            double ddx = (450 * 0.1) * cssn.x, ddy = (450 * 0.1) * cssn.y;
+            double fx = floor(ddx), fy = floor(ddy);
+            spawnP = at | (fx == ddx ? B_XEXACT : 0u) | (fy == ddy ? B_YEXACT : 0u);
+            spawnD = (int)fx + (int)fy * 65536;
+        }
+    }
+}
+
 template <int N, bool CONT>
 __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lane<N> &s, int adisc,
                                            const double (&a)[3], double spread_u, bool no_actions, TickCtx &c) {
@@ -481,50 +534,8 @@ __device__ __forceinline__ void tick_begin(const Params &p, const Geo<N> &g, Lan
     s.tick += adv ? 1 : 0;                                              // :316
     c.time_tie = adv && s.tick >= p.tie_tick;                           // :319-323
     c.run = adv && !c.time_tie;
-
     // ---- actions of the planes that are alive, :325-329 + process_action :383-424 -----------
-    const int x0 = s.x, y0 = s.y;
-    const double d0 = s.dir;
-    bool shoot = false;
-    if (c.run && s.hp > 0) {
-        double mdir = s.dir, speed = 215;
-        bool move = true;
-        if (CONT) {
-            speed = ((a[0] + 1) / 2) * (275 - 200) + 200;
-        } else {
-            move = adisc >= 0 && adisc <= 3;
-            shoot = adisc == 1;
-            if (adisc == 2) mdir = plane_rotate(s.dir, 15);
-            if (adisc == 3) mdir = plane_rotate(s.dir, -15);
-        }
-        if (move) plane_forward<CONT>(s.x, s.y, mdir, speed, p.exact_trig != 0);
-        if (CONT) { s.dir = plane_rotate(s.dir, a[1] * 35); shoot = a[2] > 0; }
-        else s.dir = mdir;
-    }
-    // Bullet.__init__ -- sprites.py:293-318.  From here on the bullet is integer: its per-update
-    // displacement d = 45*cos/sin is constant, and trunc(int + d) == int + floor(d) except that
-    // a result in (-1,0) truncates to 0 (flagged "exact" when d itself is an integer).
-    c.spawnP = 0; c.spawnD = 0;
-    if (shoot) {
-        const double bdir = d0 + (spread_u * 8 - 4);
-        const uint32_t at = (((uint32_t)x0 | ((uint32_t)y0 << 16)) + B_BIAS) | B_VALID;
-        bool done = false;
-        if (CONT && !p.exact_trig) {  // fp32 speculation, see cos_sin_fast: a guarded floor is never an exact integer
-            float cs, sn;
-            cos_sin_fast(bdir, cs, sn);
-            int fx, fy;
-            const bool okx = floor_guarded(45.0f * cs, fx), oky = floor_guarded(45.0f * sn, fy);
-            done = okx && oky;
-            c.spawnP = at; c.spawnD = fx + fy * 65536;
-        }
-        if (!done) {
-            double2 cssn = cos_sin_dir(bdir);
-            double ddx = (450 * 0.1) * cssn.x, ddy = (450 * 0.1) * cssn.y;
-            double fx = floor(ddx), fy = floor(ddy);
-            c.spawnP = at | (fx == ddx ? B_XEXACT : 0u) | (fy == ddy ? B_YEXACT : 0u);
-            c.spawnD = (int)fx + (int)fy * 65536;
-        }
-    }
+    plane_action<CONT>(p, s.x, s.y, s.dir, c.run && s.hp > 0, adisc, a, spread_u, c.spawnP, c.spawnD);
 }
 
 // One Bullet.update (sprites.py:321-351) up to the plane test, on the packed words.  `age` counts
@@ -646,15 +657,22 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
                     cm |= (rect_hit(Pp - w.plane[eb + j], 55u, 50u) ? 1u : 0u) << j;
                 }
                 M += 1u << 28;
-                if (cm) atomicAdd(&w.hits[eb + __ffs(cm) - 1], 1u);
             }
             if (code) { atomicOr(&w.ev[owner], code << (2 * ai)); keep = false; }
         }
         const unsigned kb = __ballot_sync(FULL, keep);
         const int nidx = out + __popc(kb & lt);
-        if (keep) {
-            w.ent[nidx] = make_uint2(P, M);             // nidx <= idx: never ahead of a read
-            if (cm) { atomicOr(&w.cand[owner], 1u << ai); w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm; }
+        if (keep) w.ent[nidx] = make_uint2(P, M);       // nidx <= idx: never ahead of a read
+#ifndef BS_DENSE_PREDICATED
+        // An overlap with a plane is rare (about one bullet per warp-tick): a warp-uniform branch around its
+        // bookkeeping instead of ~20 predicated instructions in every pass (r2a: 39 of 504 per warp-tick).
+        if (__any_sync(FULL, cm != 0))
+#endif
+        if (cm) {                                       // (cm != 0 implies keep: the bullet flew on)
+            const int eb = w.baseT[owner] >> 27;
+            atomicAdd(&w.hits[eb + __ffs(cm) - 1], 1u);
+            atomicOr(&w.cand[owner], 1u << ai);
+            w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm;
         }
         out += __popc(kb);
     }
