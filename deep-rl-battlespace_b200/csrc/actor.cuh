@@ -78,37 +78,42 @@ __device__ __forceinline__ void coop_copy(float *dst, const float *src, int n) {
 
 __device__ __forceinline__ float4 lds4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
 
-// acc[r][c] += a[r] * w[c] for the thread's 8 x 8 block
-__device__ __forceinline__ void outer8x8(float (&acc)[8][8], const float4 &alo, const float4 &ahi, const float4 &wlo,
+// The 8 x 8 block is held as 8 x 4 float2 (column pairs) and updated with the packed fp32 FMA of sm_100
+// (FFMA2: two IEEE fp32 FMAs per lane and instruction, one operand may be a broadcast scalar): the products are
+// the same as with scalar fmaf, in the same order, but a k-step issues 32 instructions instead of 64.  The
+// kernel was bound by instruction issue with FFMA at 69 % of the instructions (profiles/r2a_actor_raw.txt: FMA
+// pipe 49 % busy); packed, the FMA pipe itself becomes the limiter.
+// acc[r][2q..2q+1] += a[r] * w[2q..2q+1]
+__device__ __forceinline__ void outer8x8(float2 (&acc)[8][4], const float4 &alo, const float4 &ahi, const float4 &wlo,
                                          const float4 &whi) {
     const float a[8] = {alo.x, alo.y, alo.z, alo.w, ahi.x, ahi.y, ahi.z, ahi.w};
-    const float w[8] = {wlo.x, wlo.y, wlo.z, wlo.w, whi.x, whi.y, whi.z, whi.w};
+    const float2 w[4] = {make_float2(wlo.x, wlo.y), make_float2(wlo.z, wlo.w), make_float2(whi.x, whi.y), make_float2(whi.z, whi.w)};
 #pragma unroll
     for (int r = 0; r < 8; ++r)
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[r][c] = fmaf(a[r], w[c], acc[r][c]);
+        for (int q = 0; q < 4; ++q) acc[r][q] = __ffma2_rn(make_float2(a[r], a[r]), w[q], acc[r][q]);
 }
 
-__device__ __forceinline__ void init_bias(float (&acc)[8][8], const float *b, int tc) {
+__device__ __forceinline__ void init_bias(float2 (&acc)[8][4], const float *b, int tc) {
     const float4 lo = lds4(b + tc * 4), hi = lds4(b + 32 + tc * 4);
-    const float w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    const float2 w[4] = {make_float2(lo.x, lo.y), make_float2(lo.z, lo.w), make_float2(hi.x, hi.y), make_float2(hi.z, hi.w)};
 #pragma unroll
     for (int r = 0; r < 8; ++r)
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[r][c] = w[c];
+        for (int q = 0; q < 4; ++q) acc[r][q] = w[q];
 }
 
 // relu(LayerNorm(row)) for the 8 rows of the thread's block, then staged as H[col][row]
-__device__ __forceinline__ void ln_relu_store(float (&acc)[8][8], const float *g, const float *b, float *H, int tc, int rq) {
+__device__ __forceinline__ void ln_relu_store(float2 (&acc)[8][4], const float *g, const float *b, float *H, int tc, int rq) {
     const float4 glo = lds4(g + tc * 4), ghi = lds4(g + 32 + tc * 4), blo = lds4(b + tc * 4), bhi = lds4(b + 32 + tc * 4);
-    const float gg[8] = {glo.x, glo.y, glo.z, glo.w, ghi.x, ghi.y, ghi.z, ghi.w};
-    const float bb[8] = {blo.x, blo.y, blo.z, blo.w, bhi.x, bhi.y, bhi.z, bhi.w};
+    const float2 gg[4] = {make_float2(glo.x, glo.y), make_float2(glo.z, glo.w), make_float2(ghi.x, ghi.y), make_float2(ghi.z, ghi.w)};
+    const float2 bb[4] = {make_float2(blo.x, blo.y), make_float2(blo.z, blo.w), make_float2(bhi.x, bhi.y), make_float2(bhi.z, bhi.w)};
     float mean[8], rstd[8];
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
-        float s = 0.0f;
+        float s = 0.0f;   // (left to right, like the scalar version: the completed_model check sits within 2 % of its bound)
 #pragma unroll
-        for (int c = 0; c < 8; ++c) s += acc[r][c];
+        for (int q = 0; q < 4; ++q) { s += acc[r][q].x; s += acc[r][q].y; }
         mean[r] = s;
     }
 #pragma unroll
@@ -118,9 +123,13 @@ __device__ __forceinline__ void ln_relu_store(float (&acc)[8][8], const float *g
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         mean[r] *= 1.0f / AH;
+        const float2 nm = make_float2(-mean[r], -mean[r]);
         float v = 0.0f;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) { const float d = acc[r][c] - mean[r]; v = fmaf(d, d, v); }
+        for (int q = 0; q < 4; ++q) {
+            acc[r][q] = __fadd2_rn(acc[r][q], nm);                                                      // acc <- x - mean
+            v = fmaf(acc[r][q].x, acc[r][q].x, v); v = fmaf(acc[r][q].y, acc[r][q].y, v);
+        }
         rstd[r] = v;
     }
 #pragma unroll
@@ -129,15 +138,27 @@ __device__ __forceinline__ void ln_relu_store(float (&acc)[8][8], const float *g
         for (int r = 0; r < 8; ++r) rstd[r] += __shfl_xor_sync(FULL, rstd[r], m);
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
-        const float rs = 1.0f / sqrtf(rstd[r] * (1.0f / AH) + LN_EPS);
+        // 1 / sqrt(var + eps): MUFU.RSQ (2 ulp) + one Newton step = the correctly rounded value to within 1 ulp in 5
+        // instructions; the IEEE sqrt + division pair it replaces was 7 % of the kernel's instructions (r2e).  The
+        // raw rsqrtf alone is not enough for the completed_model check (logits up to +-80 amplify the error).
+        const float var = rstd[r] * (1.0f / AH) + LN_EPS;
+        const float y0 = rsqrtf(var);
+        const float rs = fmaf(y0, fmaf(-0.5f * var, y0 * y0, 0.5f), y0);
+        const float2 rs2 = make_float2(rs, rs);
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[r][c] = fmaxf(fmaf((acc[r][c] - mean[r]) * rs, gg[c], bb[c]), 0.0f);
+        for (int q = 0; q < 4; ++q) {
+            const float2 y = __ffma2_rn(__fmul2_rn(acc[r][q], rs2), gg[q], bb[q]);
+            acc[r][q] = make_float2(fmaxf(y.x, 0.0f), fmaxf(y.y, 0.0f));
+        }
     }
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         const int col = (c < 4 ? 0 : 28) + tc * 4 + c;  // columns tc*4..+3 and 32+tc*4..+3
-        *reinterpret_cast<float4 *>(H + col * HP + rq) = make_float4(acc[0][c], acc[1][c], acc[2][c], acc[3][c]);
-        *reinterpret_cast<float4 *>(H + col * HP + rq + 16) = make_float4(acc[4][c], acc[5][c], acc[6][c], acc[7][c]);
+        const int q = c >> 1;
+#define ACC_AT(r) ((c & 1) ? acc[r][q].y : acc[r][q].x)
+        *reinterpret_cast<float4 *>(H + col * HP + rq) = make_float4(ACC_AT(0), ACC_AT(1), ACC_AT(2), ACC_AT(3));
+        *reinterpret_cast<float4 *>(H + col * HP + rq + 16) = make_float4(ACC_AT(4), ACC_AT(5), ACC_AT(6), ACC_AT(7));
+#undef ACC_AT
     }
 }
 
@@ -193,6 +214,9 @@ __global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
     asm volatile("griddepcontrol.launch_dependents;");
     fetch(blockIdx.x);
     __syncthreads();      // parameters staged (the only block barrier)
+    // (Measured and not kept, r2f: 32-row units handed out warp by warp from a device counter, every block resident for
+    // the whole launch -- the kernel alone 36.9 instead of 38.2 us, but the config-5 tick 65.9 instead of 61.6 us: blocks
+    // that never exit leave no room for the next grid's blocks to start under programmatic dependent launch.)
     for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const long long e = tile * TM + tid;
         const bool ok = e < aa.E;
@@ -200,7 +224,7 @@ __global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
         for (int c = 0; c < L; ++c) Os[c * TM + tid] = onext[c];
         __syncwarp();     // the warp's 32 obs rows are staged; its H rows of the previous tile are free
         fetch(tile + gridDim.x);
-        float acc[8][8];
+        float2 acc[8][4];
         // ---- fc1 -----------------------------------------------------------------------------------
         init_bias(acc, sm + S::B1, tc);
 #pragma unroll
@@ -217,16 +241,15 @@ __global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
         ln_relu_store(acc, sm + S::G2, sm + S::E2, H, tc, rq);
         __syncwarp();
         // ---- pi + tanh (+ OU noise, clamp): one row per thread -------------------------------------
-        float pi[4];
-#pragma unroll
-        for (int a = 0; a < 4; ++a) pi[a] = sm[S::B3 + a];
+        float2 p01 = make_float2(sm[S::B3 + 0], sm[S::B3 + 1]), p23 = make_float2(sm[S::B3 + 2], sm[S::B3 + 3]);
 #pragma unroll 16
         for (int j = 0; j < AH; ++j) {
             const float x = H[j * HP + tid];
-            const float4 w = lds4(sm + S::W3T + j * 4);
-            pi[0] = fmaf(w.x, x, pi[0]); pi[1] = fmaf(w.y, x, pi[1]); pi[2] = fmaf(w.z, x, pi[2]);
-            if (A == 4) pi[3] = fmaf(w.w, x, pi[3]);
+            const float4 w = lds4(sm + S::W3T + j * 4);   // (column 3 of a 3-action head is zero)
+            p01 = __ffma2_rn(make_float2(x, x), make_float2(w.x, w.y), p01);
+            p23 = __ffma2_rn(make_float2(x, x), make_float2(w.z, w.w), p23);
         }
+        const float pi[4] = {p01.x, p01.y, p23.x, p23.y};
         if (ok) {
             const long long orow = (e * aa.n_team + k) * A;
             float nz[4] = {0.0f, 0.0f, 0.0f, 0.0f};
