@@ -173,8 +173,15 @@ __device__ __forceinline__ void lane_policy_philox(const Params &p, const Geo<N>
 #ifndef STEP_MIN_BLOCKS
 #define STEP_MIN_BLOCKS (768 / STEP_BLOCK)
 #endif
-template <int N, bool CONT>
-__global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Params p, StepArgs sa) {
+#ifndef STEP_MIN_BLOCKS_LEAN
+#define STEP_MIN_BLOCKS_LEAN (1024 / STEP_BLOCK)
+#endif
+// LEAN = plain bs_step (Mode A): both teams' actions from the caller, no replay rows, no auto-reset, no in-kernel policy,
+// no obs_in.  The general kernel needs 80 registers (24 resident warps per SM); without those paths the same tick fits
+// the register budget of 32 resident warps, which is what this latency-bound kernel lacks (profiles/r2a_step_raw.txt:
+// issue slots 55 % busy, 3.5 warps per issue waiting on memory).
+template <int N, bool CONT, bool LEAN>
+__global__ void __launch_bounds__(STEP_BLOCK, LEAN ? STEP_MIN_BLOCKS_LEAN : STEP_MIN_BLOCKS) step_kernel(Params p, StepArgs sa) {
     constexpr int P = 2 * N, L = 3 * N + 2;
     __shared__ WarpPool pools[STEP_BLOCK / 32];
     WarpPool &w = pools[threadIdx.x >> 5];
@@ -190,12 +197,14 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     int cnt;
     pool_load(p, gw, gw < p.W, g.lane(), w, cnt);
     pool_publish_base<N>(g, s, w);
+    // (Measured and not kept, r2i: one prefetch.global.L2 per lane for the lines of the block that will take over this
+    // block's slot -- 431.9 vs 431.2 us at 1,048,576 envs: the wait on the first loads is not the DRAM leg.)
 
     float o[L];
-    const bool writer = g.valid() && sa.rp.capacity > 0 && g.team() == sa.act_team;
+    const bool writer = !LEAN && g.valid() && sa.rp.capacity > 0 && g.team() == sa.act_team;
     long long row = 0;
-    if (sa.rp.capacity > 0) row = (sa.cursor_mod + g.e() % sa.rp.capacity) % sa.rp.capacity;
-    const bool need_obs = sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT || sa.rp.capacity > 0;  // kernel-uniform
+    if (!LEAN && sa.rp.capacity > 0) row = (sa.cursor_mod + g.e() % sa.rp.capacity) % sa.rp.capacity;
+    const bool need_obs = !LEAN && (sa.pol[0] >= POL_INSTINCT || sa.pol[1] >= POL_INSTINCT || sa.rp.capacity > 0);  // kernel-uniform
     if (need_obs && sa.obs_in != nullptr) {
         const float *src = sa.obs_in + ((g.valid() ? g.e() : 0) * P + g.i()) * L;
 #pragma unroll
@@ -207,7 +216,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     }
 
     // external actions
-    const int pol = g.team() ? sa.pol[1] : sa.pol[0];  // (a dynamic index would make the compiler copy the parameter struct to local memory)
+    const int pol = LEAN ? (int)POL_EXTERNAL : (g.team() ? sa.pol[1] : sa.pol[0]);  // (a dynamic index would make the compiler copy the parameter struct to local memory)
     const bool ext = g.valid() && pol == POL_EXTERNAL && sa.dtype != ACT_NONE;
     int adisc = 0;
     double a[3] = {0, 0, 0}, spread_u = 0;
@@ -268,7 +277,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     }
     double rew;
     Tally tl;
-    const bool want_obs = sa.obs != nullptr || sa.rp.capacity > 0;  // kernel-uniform
+    const bool want_obs = sa.obs != nullptr || (!LEAN && sa.rp.capacity > 0);  // kernel-uniform
     {
         TickCtx c;
         tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, sa.dtype == ACT_NONE, c);
@@ -304,9 +313,9 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
     }
     // auto-reset (the game loop's `env.reset()` for the next game, main.py:148): rewards, dones,
     // env_done and winner below still describe the finished game; obs is the new game's first one.
-    const bool fresh = sa.auto_reset && g.valid() && s.env_done;
+    const bool fresh = !LEAN && sa.auto_reset && g.valid() && s.env_done;
     const int out_done = s.env_done, out_hp = s.hp, out_winner = s.winner;
-    if (sa.auto_reset && __any_sync(FULL, fresh)) {
+    if (!LEAN && sa.auto_reset && __any_sync(FULL, fresh)) {
         if (fresh) { reset_lane(p, g, s, false, nullptr); ret0 = ret1 = 0; }
         pool_filter(w, cnt, __ballot_sync(FULL, fresh), g.lane());  // the finished games' bullets vanish, battle_env.py:272
         gather(g, s);
@@ -327,7 +336,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) step_kernel(Param
             if (sa.winner) sa.winner[g.e()] = (int8_t)out_winner;
         }
     }
-    store_lane(p, g, s, ret0, ret1, sa.auto_reset != 0);
+    store_lane(p, g, s, ret0, ret1, !LEAN && sa.auto_reset != 0);
     pool_store(p, gw, gw < p.W, g.lane(), w, cnt);
     flush_tally<N>(p, tl);
 }
@@ -855,8 +864,15 @@ int bs_reset(bs_handle *h, const uint8_t *env_mask, const int32_t *draws, float 
 static int launch_step(bs_handle *h, const StepArgs &sa, cudaStream_t st) {
     { int rc = ensure_bullets(h, FMT_POOLS, st); if (rc) return rc; }
     const int grid = grid_for_envs(h->E, h->N, STEP_BLOCK);
-    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true>, grid, STEP_BLOCK, st, h->p, sa))); }
-    else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false>, grid, STEP_BLOCK, st, h->p, sa))); }
+    const bool lean = sa.pol[0] == POL_EXTERNAL && sa.pol[1] == POL_EXTERNAL && sa.rp.capacity == 0 && !sa.auto_reset &&
+                      sa.obs_in == nullptr && sa.act_agents == h->P && getenv("BS_STEP_GENERAL") == nullptr;
+    if (lean) {
+        if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true, true>, grid, STEP_BLOCK, st, h->p, sa))); }
+        else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false, true>, grid, STEP_BLOCK, st, h->p, sa))); }
+        return BS_OK;
+    }
+    if (h->cont) { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, true, false>, grid, STEP_BLOCK, st, h->p, sa))); }
+    else { DISPATCH_N(h->N, CU(launch(h, step_kernel<N_, false, false>, grid, STEP_BLOCK, st, h->p, sa))); }
     return BS_OK;
 }
 
