@@ -518,6 +518,18 @@ __global__ void __launch_bounds__(128) replay_sample_kernel(SampleArgs sa) {
     }
 }
 
+// State export / import move only the LIVE pool entries: pack copies each warp's cnt entries to off[w].. of a
+// dense buffer (one warp per pool, coalesced), unpack is the inverse.  (Round 1 copied the whole W x 384-entry
+// pool array: 1.2 GB for a million 5v5 envs to export a few live bullets per env.)
+__global__ void __launch_bounds__(128) pool_pack_kernel(const uint2 *pool, const int *cnt, const long long *off, long long W, uint2 *dense, int unpack) {
+    const long long wv = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (wv >= W) return;
+    const int lane = threadIdx.x & 31, n = cnt[wv];
+    uint2 *a = const_cast<uint2 *>(pool) + wv * POOL_CAP;
+    uint2 *b = dense + off[wv];
+    for (int q = lane; q < n; q += 32) { if (unpack) a[q] = b[q]; else b[q] = a[q]; }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host side: handle + C ABI
 // ------------------------------------------------------------------------------------------------
@@ -559,8 +571,8 @@ struct bs_handle {
     int64_t *pinned_stats = nullptr; // [2][8] pinned host memory
     int inflight = 0, next_buf = 0;  // calls begun and not yet ended (0..2); staging buffer of the next call
     // device staging for *_host calls (grown on demand)
-    void *stage[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t stage_sz[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    void *stage[12] = {};            // slots 10, 11: offsets / dense entries of bs_get_state, bs_set_state
+    size_t stage_sz[12] = {};
 };
 
 struct DeviceGuard {
@@ -1059,9 +1071,39 @@ int bs_render(bs_handle *h, int64_t env, const bs_sprites *sprites, uint8_t *rgb
     if (!sprites->plane[0] || !sprites->plane[1] || !sprites->base[0] || !sprites->base[1]) return fail(BS_E_INVALID, "null sprite");
     DeviceGuard guard(h->device);
     if (sprites->n_explosions < 0) return fail(BS_E_INVALID, "n_explosions must be >= 0");
-    RenderArgs ra{env, {sprites->plane[0], sprites->plane[1]}, {sprites->base[0], sprites->base[1]}, rgb,
-                  sprites->explosion_img, sprites->explosions, sprites->n_explosions};
-    { int rc = ensure_bullets(h, FMT_POOLS, (cudaStream_t)stream); if (rc) return rc; }
+    RenderArgs ra{};
+    ra.env = env; ra.plane_img[0] = sprites->plane[0]; ra.plane_img[1] = sprites->plane[1];
+    ra.base_img[0] = sprites->base[0]; ra.base_img[1] = sprites->base[1]; ra.rgb = rgb;
+    ra.expl_img = sprites->explosion_img; ra.expl = sprites->explosions; ra.n_expl = sprites->n_explosions;
+    {   // pygame.transform.rotate parameters of the env's planes, with the host libm like pygame (render.cuh PlaneRot)
+        uint32_t pos[16]; double dir[16];
+        cudaStream_t st = (cudaStream_t)stream;
+        CU(cudaMemcpyAsync(pos, h->p.plane_pos + env * h->P, (size_t)h->P * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(dir, h->p.plane_dir + env * h->P, (size_t)h->P * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        for (int i = 0; i < h->P; ++i) {
+            PlaneRot &r = ra.rot[i];
+            const int w = PLANE_W, hgt = PLANE_H, cx = (int)(pos[i] & 0xffff), cy = (int)(pos[i] >> 16);
+            const double angle = dir[i];
+            if (std::fmod(angle, 90.0) == 0.0) {           // surf_rotate: if (!(fmod(angle, 90))) -> rotate90
+                int turns = ((int)(angle / 90.0)) % 4;
+                if (turns < 0) turns += 4;
+                r.turns = turns; r.nx = (turns % 2) ? hgt : w; r.ny = (turns % 2) ? w : hgt;
+                r.ax = r.ay = r.isin = r.icos = 0;
+            } else {
+                volatile double radangle = angle * .01745329251994329;
+                volatile double sangle = std::sin(radangle), cangle = std::cos(radangle);
+                const double x = w, y = hgt, cxr = cangle * x, cyr = cangle * y, sxr = sangle * x, syr = sangle * y;
+                r.nx = (int)std::fmax(std::fmax(std::fmax(std::fabs(cxr + syr), std::fabs(cxr - syr)), std::fabs(-cxr + syr)), std::fabs(-cxr - syr));
+                r.ny = (int)std::fmax(std::fmax(std::fmax(std::fabs(sxr + cyr), std::fabs(sxr - cyr)), std::fabs(-sxr + cyr)), std::fabs(-sxr - cyr));
+                r.isin = (int)(sangle * 65536); r.icos = (int)(cangle * 65536);
+                r.ax = ((r.nx) << 15) - (int)(cangle * ((r.nx - 1) << 15)) + ((w - r.nx) * 32768);
+                r.ay = ((r.ny) << 15) - (int)(sangle * ((r.nx - 1) << 15)) + ((hgt - r.ny) * 32768);
+                r.turns = -1;
+            }
+            r.left = cx - (r.nx >> 1); r.top = cy - (r.ny >> 1);   // Rect.center setter: x = cx - (w >> 1)
+        }
+    }
     const int grid = (R_W * R_H + 255) / 256;
     DISPATCH_N(h->N, render_kernel<N_><<<grid, 256, 0, (cudaStream_t)stream>>>(h->p, ra));
     CU(cudaGetLastError());
@@ -1108,19 +1150,30 @@ int bs_get_state(bs_handle *h, const bs_state_view *v) {
     CU(cudaDeviceSynchronize());
     const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
     std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E), epi((size_t)E);
-    std::vector<uint2> pool((size_t)h->W * POOL_CAP);
     std::vector<int> pcnt((size_t)h->W);
     std::vector<double> dir(EP), ret((size_t)E * 2);
     std::vector<int8_t> hp(EP);
     std::vector<int16_t> bhp((size_t)E * 2);
     const Params &p = h->p;
+    // live pool entries only: counts -> offsets (host scan) -> dense device buffer -> host
+    CU(cudaMemcpy(pcnt.data(), p.pool_cnt, pcnt.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    std::vector<long long> poff((size_t)h->W + 1, 0);
+    for (int64_t wv = 0; wv < h->W; ++wv) poff[wv + 1] = poff[wv] + (pcnt[wv] < 0 ? 0 : (pcnt[wv] > POOL_CAP ? POOL_CAP : pcnt[wv]));
+    std::vector<uint2> pool((size_t)poff[h->W] + 1);
+    {
+        void *d_off = nullptr, *d_dense = nullptr;
+        int rc = stage_buf(h, 10, poff.size() * sizeof(long long), &d_off); if (rc) return rc;
+        rc = stage_buf(h, 11, pool.size() * sizeof(uint2), &d_dense); if (rc) return rc;
+        CU(cudaMemcpy(d_off, poff.data(), poff.size() * sizeof(long long), cudaMemcpyHostToDevice));
+        pool_pack_kernel<<<(unsigned)((h->W * 32 + 127) / 128), 128>>>(p.pool, p.pool_cnt, (const long long *)d_off, h->W, (uint2 *)d_dense, 0);
+        CU(cudaGetLastError());
+        CU(cudaMemcpy(pool.data(), d_dense, (size_t)poff[h->W] * sizeof(uint2), cudaMemcpyDeviceToHost));
+    }
     CU(cudaMemcpy(pos.data(), p.plane_pos, EP * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(dir.data(), p.plane_dir, EP * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(hp.data(), p.plane_hp, EP, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(bpos.data(), p.base_pos, (size_t)E * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(bhp.data(), p.base_hp, (size_t)E * 4, cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(pool.data(), p.pool, pool.size() * sizeof(uint2), cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(pcnt.data(), p.pool_cnt, pcnt.size() * sizeof(int), cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(meta.data(), p.meta, (size_t)E * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(epi.data(), p.episode, (size_t)E * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(ret.data(), p.ret, (size_t)E * 16, cudaMemcpyDeviceToHost));
@@ -1136,8 +1189,8 @@ int bs_get_state(bs_handle *h, const bs_state_view *v) {
     }
     // pool entry -> (env, plane, age): owner lane = sub * 2N + plane, env = warp * K + sub; exported index = age - 1
     for (int64_t wv = 0; wv < h->W; ++wv)
-        for (int q = 0; q < pcnt[wv]; ++q) {
-            const uint2 en = pool[(size_t)wv * POOL_CAP + q];
+        for (int q = 0; q < (int)(poff[wv + 1] - poff[wv]); ++q) {
+            const uint2 en = pool[(size_t)poff[wv] + q];
             const uint32_t ps = en.x, M = en.y;
             if (!(ps & B_VALID)) continue;
             const int owner = (M >> 23) & 31, age = (int)(M >> 28), sub = owner / P, i = owner - sub * P;
@@ -1180,7 +1233,8 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     CU(cudaDeviceSynchronize());
     const int64_t E = h->E; const int P = h->P; const size_t EP = (size_t)E * P;
     std::vector<uint32_t> pos(EP), bpos((size_t)E * 2), meta((size_t)E);
-    std::vector<uint2> pool((size_t)h->W * POOL_CAP);
+    std::vector<uint2> pool;          // dense: warp after warp
+    std::vector<long long> poff((size_t)h->W + 1, 0);
     std::vector<int> pcnt((size_t)h->W, 0);
     // the observation tables (and the packed 11/10-bit plane words) cover on-field points only
     for (size_t a = 0; a < EP; ++a) {
@@ -1194,7 +1248,7 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
             return fail(BS_E_INVALID, "bs_set_state: base position outside the 1200x800 field");
     for (size_t a = 0; a < EP; ++a) pos[a] = (uint32_t)(uint16_t)v->plane_x[a] | ((uint32_t)(uint16_t)v->plane_y[a] << 16);
     // bullets -> the warp pools, oldest first (the order inside a pool carries no meaning)
-    for (int64_t wv = 0; wv < h->W; ++wv)
+    for (int64_t wv = 0; wv < h->W; poff[wv + 1] = (long long)pool.size(), ++wv)
         for (int o = SLOTS - 2; o >= 0; --o)          // age 12 never survives a tick
             for (int owner = 0; owner < h->K * P; ++owner) {
                 const int sub = owner / P, i = owner - sub * P;
@@ -1208,7 +1262,7 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
                                     ((vel[2] & 2) ? B_XEXACT : 0u) | ((vel[2] & 4) ? B_YEXACT : 0u);
                 const int32_t dl = (int32_t)vel[0] + (int32_t)vel[1] * 65536;
                 const uint32_t M = ((uint32_t)dl & 0x7fffffu) | ((uint32_t)owner << 23) | ((uint32_t)(o + 1) << 28);
-                pool[(size_t)wv * POOL_CAP + pcnt[wv]++] = make_uint2(Pw, M);
+                pool.push_back(make_uint2(Pw, M)); pcnt[wv] += 1;
             }
     for (int64_t e = 0; e < E; ++e) {
         for (int t = 0; t < 2; ++t)
@@ -1221,8 +1275,17 @@ int bs_set_state(bs_handle *h, const bs_state_view *v) {
     CU(cudaMemcpy(p.plane_hp, v->plane_hp, EP, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.base_pos, bpos.data(), (size_t)E * 8, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.base_hp, v->base_hp, (size_t)E * 4, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(p.pool, pool.data(), pool.size() * sizeof(uint2), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.pool_cnt, pcnt.data(), pcnt.size() * sizeof(int), cudaMemcpyHostToDevice));
+    {
+        void *d_off = nullptr, *d_dense = nullptr;
+        int rc = stage_buf(h, 10, poff.size() * sizeof(long long), &d_off); if (rc) return rc;
+        rc = stage_buf(h, 11, (pool.size() + 1) * sizeof(uint2), &d_dense); if (rc) return rc;
+        CU(cudaMemcpy(d_off, poff.data(), poff.size() * sizeof(long long), cudaMemcpyHostToDevice));
+        if (!pool.empty()) CU(cudaMemcpy(d_dense, pool.data(), pool.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+        pool_pack_kernel<<<(unsigned)((h->W * 32 + 127) / 128), 128>>>(p.pool, p.pool_cnt, (const long long *)d_off, h->W, (uint2 *)d_dense, 1);
+        CU(cudaGetLastError());
+        CU(cudaDeviceSynchronize());
+    }
     h->bullet_fmt = FMT_POOLS;
     CU(cudaMemcpy(p.meta, meta.data(), (size_t)E * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(p.episode, v->episode, (size_t)E * 4, cudaMemcpyHostToDevice));

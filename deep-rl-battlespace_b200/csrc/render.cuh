@@ -7,11 +7,12 @@
 // caller's list of {x, y, frame}, the animation history is host-side like self.explosions), both bases with their
 // hp bar (:539-540, sprites.py:265-278), alive red then blue planes with their hp bar (:543-550,
 // sprites.py:155-178).  Sprites are RGBA images handed over by the caller (the reference's
-// assets/*.png or procedural stand-ins); a rotated sprite is sampled by inverse mapping with
-// nearest-neighbour like pygame.transform.rotate (counter-clockwise, about the rect centre).
+// assets/*.png or procedural stand-ins).  A plane sprite goes through pygame 2.1.2's transform.rotate algorithm
+// (PlaneRot below: fixed-point inverse mapping, destination size rule, rotate90 for right angles) and is blitted at
+// the rect blitRotate computes; bullets are 6 x 3 quads along their integer step (half-pixel coordinates, Q14 cos/sin:
+// the env state keeps a bullet's integer step, not its direction).
 //
-// All geometry is integer: coordinates in half-pixels, rotation by Q14 fixed-point cos/sin, so the
-// CPU restatement used by the tests reproduces every pixel bit for bit.  One thread per pixel; the
+// All geometry is integer, so the CPU restatement used by the tests reproduces every pixel bit for bit.  One thread per pixel; the
 // env's objects are staged once per block in shared memory with their bounding boxes.
 #pragma once
 #include "tick.cuh"
@@ -23,8 +24,19 @@ constexpr int PLANE_W = 50, PLANE_H = 48, BASE_W = 62, BASE_H = 62, BUL_W = 6, B
 constexpr int Q = 14;                                // fixed-point bits of cos / sin
 constexpr int EXPL_W = 64, EXPL_FRAMES = 9, MAX_EXPL = 64;   // sprites.py:392-398
 
+// pygame.transform.rotate of one plane sprite, prepared on the HOST by bs_render (sin / cos from the host libm, the
+// functions pygame's C code calls): pygame 2.1.2 src_c/transform.c, surf_rotate() (destination size nx x ny from the
+// rotated corner extents, truncated) and rotate() (16.16 fixed point: isin = (int)(sin * 65536), icos likewise, start
+// ax = (nx << 15) - (int)(cos * ((nx - 1) << 15)), ay = (ny << 15) - (int)(sin * ((nx - 1) << 15)), recentring
+// xd = (w - nx) << 15, yd = (h - ny) << 15; destination (x, y) samples source (dx >> 16, dy >> 16) with
+// dx = ax + xd + isin * (ny / 2 - y) + icos * x, dy = ay + yd - icos * (ny / 2 - y) + isin * x, transparent outside);
+// multiples of 90 degrees take rotate90()'s exact pixel permutation (turns = 0..3, else -1).  The rotated surface is
+// blitted at the rect blitRotate computes (sprites.py:13-33): centre = the plane's rect centre, i.e. left = cx - (nx >> 1).
+struct PlaneRot { int left, top, nx, ny, ax, ay, isin, icos, turns; };
+
 struct RenderArgs {
     long long env;
+    PlaneRot rot[16];              // per plane of the env
     const uint8_t *plane_img[2];   // [48][50][4] RGBA, red / blue
     const uint8_t *base_img[2];    // [62][62][4]
     uint8_t *rgb;                  // [800][1200][3]
@@ -132,7 +144,7 @@ __global__ void __launch_bounds__(256) render_kernel(Params p, RenderArgs ra) {
     const int py = pix / R_W, px_ = pix - py * R_W;
     uint8_t out[3] = {255, 255, 255};  // sprites.WHITE
 
-    auto rotated = [&](const RObj &o) {
+    auto rotated = [&](const RObj &o) {   // bullets: 6 x 3 quads along their integer step (the state keeps no bullet direction)
         if (o.kind < 0) return;
         const int dx = 2 * px_ + 1 - o.cx2, dy = 2 * py + 1 - o.cy2;   // pixel centre - sprite centre, half-pixels
         if (abs(dx) > o.rad2 || abs(dy) > o.rad2) return;
@@ -140,8 +152,23 @@ __global__ void __launch_bounds__(256) render_kernel(Params p, RenderArgs ra) {
         const int ux = dx * o.c - dy * o.s, uy = dx * o.s + dy * o.c;       // Q14 half-pixels
         const int u = (ux + (o.w << Q)) >> (Q + 1), v = (uy + (o.h << Q)) >> (Q + 1);  // floor((u/2) + w/2)
         if (u < 0 || u >= o.w || v < 0 || v >= o.h) return;
-        if (o.kind >= 2) team_colour(o.kind - 2, out);
-        else blend(out, ra.plane_img[o.kind] + (v * PLANE_W + u) * 4);
+        team_colour(o.kind - 2, out);
+    };
+    auto plane = [&](const RObj &o, const PlaneRot &r) {   // pygame.transform.rotate + blit, see PlaneRot
+        if (o.kind < 0) return;
+        const int x = px_ - r.left, y = py - r.top;
+        if (x < 0 || x >= r.nx || y < 0 || y >= r.ny) return;
+        int u, v;
+        if (r.turns >= 0) {                                 // rotate90(): dst(x, y) = src(u, v)
+            u = r.turns == 0 ? x : (r.turns == 1 ? PLANE_W - 1 - y : (r.turns == 2 ? PLANE_W - 1 - x : y));
+            v = r.turns == 0 ? y : (r.turns == 1 ? x : (r.turns == 2 ? PLANE_H - 1 - y : PLANE_H - 1 - x));
+        } else {
+            const int cyd = r.ny / 2;
+            const int sx = r.ax + r.isin * (cyd - y) + r.icos * x, sy = r.ay - r.icos * (cyd - y) + r.isin * x;
+            if (sx < 0 || sy < 0 || sx > (PLANE_W << 16) - 1 || sy > (PLANE_H << 16) - 1) return;   // bgcolor: transparent
+            u = sx >> 16; v = sy >> 16;
+        }
+        blend(out, ra.plane_img[o.kind] + (v * PLANE_W + u) * 4);
     };
     auto draw_bar = [&](const RBar &b) {
         if (b.team < 0) return;
@@ -162,7 +189,7 @@ __global__ void __launch_bounds__(256) render_kernel(Params p, RenderArgs ra) {
         if (u >= 0 && u < BASE_W && v >= 0 && v < BASE_H) blend(out, ra.base_img[t] + (v * BASE_W + u) * 4);
         draw_bar(bar[t]);
     }
-    for (int i = 0; i < P; ++i) { rotated(obj[P * SLOTS + i]); if (obj[P * SLOTS + i].kind >= 0) draw_bar(bar[2 + i]); }
+    for (int i = 0; i < P; ++i) { plane(obj[P * SLOTS + i], ra.rot[i]); if (obj[P * SLOTS + i].kind >= 0) draw_bar(bar[2 + i]); }
     uint8_t *dst = ra.rgb + (size_t)pix * 3;
     dst[0] = out[0]; dst[1] = out[1]; dst[2] = out[2];
 }

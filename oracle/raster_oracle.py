@@ -1,13 +1,31 @@
-"""TEST INFRASTRUCTURE ONLY -- CPU restatement (numpy, integer arithmetic) of the draw order of
-parallel_env.render (/root/reference/envs/battle_env.py:498-560; sprites.py:155-178 Plane.draw,
-:265-278 Base.draw, :353-360 Bullet.draw, blitRotate :13-33) for the headless frame the CUDA rasteriser
-produces.  Parity status: **unpinned** against pygame itself -- pygame.transform.rotate and the display
-are unavailable on this box; what this pins is the documented geometry (half-pixel integer coordinates,
-Q14 rotation, nearest-neighbour inverse mapping, pygame's per-pixel-alpha blend formula), pixel for
-pixel.  Explosions (Explosion.draw, sprites.py:405-419) are drawn from a caller-supplied list of
-(x, y, frame); fonts (names, winner screen) and rounded bar corners are left out on both sides.
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement (numpy, integer arithmetic) of parallel_env.render
+(/root/reference/envs/battle_env.py:498-560; sprites.py:155-178 Plane.draw, :265-278 Base.draw, :353-360
+Bullet.draw, blitRotate :13-33) for the headless frame the CUDA rasteriser produces.
+
+The pixel work of the reference is done by a third-party dependency that is absent here: **pygame==2.1.2**
+(requirements.txt:6), call sites sprites.py:29 (transform.rotate) and :161,168,265,360,414 (Surface.blit).  Its
+published algorithms are restated below, from src_c/transform.c and src_c/alphablit.c / surface.h of that release:
+  * surf_rotate(): a multiple of 90 degrees goes to rotate90() (exact pixel permutation, numturns = (angle / 90) % 4);
+    otherwise the destination is nx x ny with nx = (int)max(|cx+sy|, |cx-sy|, |-cx+sy|, |-cx-sy|), ny likewise from
+    (sx, cy), where (cx, cy, sx, sy) = (cos*w, cos*h, sin*w, sin*h) and radangle = angle * .01745329251994329;
+  * rotate(): 16.16 fixed-point nearest-neighbour inverse mapping -- isin = (int)(sin * 65536), icos = (int)(cos * 65536),
+    ax = (nx << 15) - (int)(cos * ((nx - 1) << 15)), ay = (ny << 15) - (int)(sin * ((nx - 1) << 15)),
+    xd = (w - nx) << 15, yd = (h - ny) << 15; row y starts at dx = ax + isin * (ny / 2 - y) + xd,
+    dy = ay - icos * (ny / 2 - y) + yd and steps (icos, isin) per destination pixel; a pixel whose (dx, dy) leaves
+    [0, (w << 16) - 1] x [0, (h << 16) - 1] takes the background (transparent for an SRCALPHA surface);
+  * the blit of an SRCALPHA surface onto the opaque display: ALPHA_BLEND, d = ((d << 8) + (s - d) * a + s) >> 8;
+  * blitRotate (sprites.py:13-33) with the even-sized 50 x 48 sprite: the rotated surface's rect is centred on the
+    plane's rect centre, Rect.center setter x = cx - (w >> 1).
+Parity status: **unpinned** -- pygame itself (display, transform) is unavailable on this box, so this restatement
+could not be run against it; the CUDA kernel is checked against this file pixel for pixel.  Not restated: fonts
+(plane names sprites.py:163-168, winner text battle_env.py:426-447: no font rasteriser here), border_radius = 3 of
+the hit-point bars (square corners on both sides), and a bullet's exact direction (the env state keeps a bullet's
+integer step, so its 6 x 3 quad is drawn along that step with Q14 fixed point instead of through transform.rotate).
+Explosions (Explosion.draw, sprites.py:405-419) are drawn from a caller-supplied list of (x, y, frame).
 
 Input: the env state as returned by parallel_env.get_state() for ONE env, and the four RGBA sprites."""
+import math
+
 import numpy as np
 
 W, H, Q = 1200, 800, 14
@@ -39,6 +57,45 @@ def _rotated(img, cx, cy, c, s, w, h, sprite=None, colour=None):
         img[ys[ok], xs[ok]] = colour
     else:
         _blend(img, ys[ok], xs[ok], sprite[v[ok], u[ok]])
+
+
+def pygame_rotate(src, angle):
+    """pygame.transform.rotate(surface, angle) for an RGBA uint8 image [h, w, 4] (see the module docstring)."""
+    h, w = src.shape[:2]
+    if math.fmod(angle, 90.0) == 0.0:                                   # rotate90()
+        turns = int(angle / 90.0) % 4 if angle >= 0 else -(int(-angle / 90.0) % 4)   # C: (int)(angle / 90) % 4
+        if turns < 0:
+            turns += 4
+        nx, ny = (h, w) if turns % 2 else (w, h)
+        y, x = np.mgrid[0:ny, 0:nx]
+        u = [x, w - 1 - y, w - 1 - x, y][turns]
+        v = [y, x, h - 1 - y, h - 1 - x][turns]
+        return src[v, u].copy()
+    rad = angle * .01745329251994329
+    sangle, cangle = math.sin(rad), math.cos(rad)
+    cx, cy, sx, sy = cangle * w, cangle * h, sangle * w, sangle * h
+    nx = int(max(abs(cx + sy), abs(cx - sy), abs(-cx + sy), abs(-cx - sy)))
+    ny = int(max(abs(sx + cy), abs(sx - cy), abs(-sx + cy), abs(-sx - cy)))
+    isin, icos = int(sangle * 65536), int(cangle * 65536)
+    ax = (nx << 15) - int(cangle * ((nx - 1) << 15))
+    ay = (ny << 15) - int(sangle * ((nx - 1) << 15))
+    xd, yd = (w - nx) * 32768, (h - ny) * 32768
+    y, x = np.mgrid[0:ny, 0:nx].astype(np.int64)
+    cyd = ny // 2
+    dx = ax + isin * (cyd - y) + xd + icos * x
+    dy = ay - icos * (cyd - y) + yd + isin * x
+    ok = (dx >= 0) & (dy >= 0) & (dx <= (w << 16) - 1) & (dy <= (h << 16) - 1)
+    dst = np.zeros((ny, nx, 4), np.uint8)                              # bgcolor: transparent
+    dst[ok] = src[dy[ok] >> 16, dx[ok] >> 16]
+    return dst
+
+
+def _blit(img, surf, left, top):
+    """Surface.blit(surf, rect) clipped to the display."""
+    ny, nx = surf.shape[:2]
+    ys, xs = np.mgrid[max(top, 0):min(top + ny, H), max(left, 0):min(left + nx, W)]
+    if ys.size:
+        _blend(img, ys, xs, surf[ys - top, xs - left])
 
 
 def _bar(img, cx, cy, dy, hp, colour):
@@ -84,8 +141,7 @@ def render(state, e, n_agents, plane_sprites, base_sprites, explosion_frames=Non
         if hp <= 0:
             continue
         x, y, d = int(state["plane_x"][e, i]), int(state["plane_y"][e, i]), float(state["plane_dir"][e, i])
-        rad = d * (np.pi / 180.0)
-        c, s = int(np.rint(np.cos(rad) * (1 << Q))), int(np.rint(np.sin(rad) * (1 << Q)))
-        _rotated(img, x, y, c, s, 50, 48, sprite=plane_sprites[i >= N])
+        rot = pygame_rotate(plane_sprites[i >= N], d)                 # blitRotate, sprites.py:13-33,160-161
+        _blit(img, rot, x - (rot.shape[1] >> 1), y - (rot.shape[0] >> 1))
         _bar(img, x, y, 35, hp, RED if i < N else BLUE)
     return img

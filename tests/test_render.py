@@ -1,6 +1,8 @@
-"""GPU: the headless CUDA rasteriser (bs_render) against the numpy restatement of the
-draw order (oracle/raster_oracle.py), pixel for pixel.  Parity against pygame itself is unpinned: the
-display and pygame.transform are unavailable on this box."""
+"""GPU: the headless CUDA rasteriser (bs_render) against oracle/raster_oracle.py, pixel for pixel.
+The oracle restates pygame 2.1.2's transform.rotate (surf_rotate / rotate / rotate90 of src_c/transform.c) and its
+SRCALPHA blit for the plane sprites, and the reference's draw order (battle_env.py:528-550).  Parity against pygame
+itself stays unpinned: the display and pygame.transform are unavailable on this box.  With
+BATTLESPACE_ASSETS=<reference>/assets the reference's own PNGs are drawn instead of the procedural stand-ins."""
 import os
 
 import numpy as np
@@ -9,7 +11,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("N,cont", [(1, False), (3, True), (5, True)])
+@pytest.mark.parametrize("N,cont", [(1, False), (2, False), (3, True), (5, True)])
 def test_frames_match_cpu_restatement(cuda_device, N, cont):
     import torch
     from battlespace import parallel_env
@@ -17,7 +19,7 @@ def test_frames_match_cpu_restatement(cuda_device, N, cont):
     import raster_oracle
     E = 64
     env = parallel_env(n_agents=N, continuous_actions=cont, n_envs=E, seed=11)
-    sp = Sprites(cuda_device)
+    sp = Sprites(cuda_device, os.environ.get("BATTLESPACE_ASSETS"))
     bad = 0
     for k in range(3):
         env.rollout(25 + 20 * k, "instinct_ff" if cont else "random", "instinct")   # bullets in flight, some damage
