@@ -633,6 +633,48 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
     __syncwarp();
     // (the caller has run gather(): enemy positions after the move, hp before the bullet loop)
     int out = 0;
+#ifndef BS_DENSE_BRANCHY
+    // Branch-free body: every lane runs the advance, the base test and the N plane tests, and the outcome is assembled
+    // with selects.  The chain miss / else base / else planes cost four divergent regions (BSSY / BRA / BSYNC, ~14
+    // instructions per pass) that almost every pass executed anyway, since some lane of 32 always takes each side.
+#pragma unroll 1
+    for (int base = 0; base < cnt_in; base += 32) {
+        const int idx = base + lane;
+        const uint2 en = w.ent[min(idx, POOL_CAP - 1)];
+        const uint32_t P0 = idx < cnt_in ? en.x : 0u;
+        uint32_t M = en.y;
+        const int owner = (M >> 23) & 31;
+        const int age = (int)(M >> 28) + 1;             // updates including this one
+        const int ai = SLOTS - age;                     // age index, 0 = oldest
+        const bool live = (P0 & B_VALID) != 0;          // dead entries (plane hits of the last tick) are squeezed out
+        const bool act = live && ((runmask >> owner) & 1u);   // the bullets of an env that did not run this tick stay put
+        const uint32_t bt = w.baseT[owner];
+        uint32_t P = P0;
+        const bool miss = bullet_advance(P, meta_dlt(M), age);
+        const bool hitb = rect_hit((P & B_POS) - (bt & 0x07ffffffu), 67u, 64u);
+        const uint32_t Pp = (P & B_POS) - PLANE_OFF;
+        const int eb = bt >> 27;
+        unsigned cm = 0;
+#pragma unroll
+        for (int j = 0; j < N; ++j) cm |= (rect_hit(Pp - w.plane[eb + j], 55u, 50u) ? 1u : 0u) << j;
+        const unsigned code = act ? (miss ? 1u : (hitb ? 2u : 0u)) : 0u;
+        if (!act || code) cm = 0;
+        if (!act) P = P0; else if (!code) M += 1u << 28;
+        if (code) atomicOr(&w.ev[owner], code << (2 * ai));
+        const bool keep = live && !code;
+        const unsigned kb = __ballot_sync(FULL, keep);
+        const int nidx = out + __popc(kb & lt);
+        if (keep) w.ent[nidx] = make_uint2(P, M);       // nidx <= idx: never ahead of a read
+        if (__any_sync(FULL, cm != 0)) {                // an overlap with a plane is rare: about one bullet per warp-tick
+            if (cm) {
+                atomicAdd(&w.hits[eb + __ffs(cm) - 1], 1u);
+                atomicOr(&w.cand[owner], 1u << ai);
+                w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm;
+            }
+        }
+        out += __popc(kb);
+    }
+#else
 #pragma unroll 1
     for (int base = 0; base < cnt_in; base += 32) {
         const int idx = base + lane;
@@ -676,6 +718,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         }
         out += __popc(kb);
     }
+#endif
     cnt = out;
     __syncwarp();
     ev = w.ev[lane];
