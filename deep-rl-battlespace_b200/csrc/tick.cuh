@@ -301,12 +301,18 @@ __device__ __forceinline__ void observe_issue(const Params &p, const Lane<N> &s,
 template <int N>
 __device__ __forceinline__ void observe_finish(const Lane<N> &s, const ObsLoads<N> &q, float (&o)[3 * N + 2]) {
     const bool me = s.hp > 0;
-    o[0] = me ? q.od[0] : -1.0f; o[1] = me ? pair_angle(q.r[0], q.neg & 1u, s.dir) : -1.0f;
+    // the angles of all N + 1 pairs first, on every lane (an unobserved pair's record is zero: harmless), then the
+    // selects: `seen ? pair_angle(..) : -1` made the compiler put a divergent region around every pair (r2l: 18
+    // control-flow instructions per warp-tick here)
+    float ang[N + 1];
+#pragma unroll
+    for (int j = 0; j <= N; ++j) ang[j] = pair_angle(q.r[j], (q.neg >> j) & 1u, s.dir);
+    o[0] = me ? q.od[0] : -1.0f; o[1] = me ? ang[0] : -1.0f;
 #pragma unroll
     for (int j = 0; j < N; ++j) {
         const bool seen = me && ((s.am >> j) & 1u);
         o[2 + 3 * j] = seen ? 1.0f : -1.0f; o[3 + 3 * j] = seen ? q.od[j + 1] : -1.0f;
-        o[4 + 3 * j] = seen ? pair_angle(q.r[j + 1], (q.neg >> (j + 1)) & 1u, s.dir) : -1.0f;
+        o[4 + 3 * j] = seen ? ang[j + 1] : -1.0f;
     }
 }
 
@@ -423,9 +429,11 @@ __device__ __forceinline__ void plane_forward(int &x, int &y, double dir, double
 
 // Plane.rotate -- sprites.py:93-103
 __device__ __forceinline__ double plane_rotate(double dir, double a) {
+    // |a| <= 35 (a clipped turn action times max_turn, or +-15) and dir in [0, 360]: the reference's two while loops
+    // (sprites.py:100-103) run at most once each; as selects they cost no divergent region
     dir += a;
-    while (dir > 360) dir -= 360;
-    while (dir < 0) dir += 360;
+    dir = dir > 360 ? dir - 360 : dir;
+    dir = dir < 0 ? dir + 360 : dir;
     return dir;
 }
 
