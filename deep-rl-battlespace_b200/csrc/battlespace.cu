@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, LEAN ? STEP_MIN_BLOCKS_LEAN : STEP
         gather(g, s);  // enemy positions after the move, hp before the bullet loop
         if (want_obs) observe_issue<N>(p, s, q);
         unsigned ev; int died_ai;
-        bullets_dense<N>(g, s, w, cnt, c, ev, died_ai);
+        bullets_dense<N, false>(g, s, w, cnt, c, ev, died_ai);
         tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
         if (want_obs) observe_finish<N>(s, q, o);
     }
@@ -352,7 +352,17 @@ template <int N, bool CONT>
 __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Params p, RolloutArgs ra) {
     constexpr int L = 3 * N + 2, A = CONT ? 3 : 4;
     __shared__ WarpPool pools[ROLLOUT_BLOCK / 32];
+#ifndef BS_POOL_REMAT
+    // The warp's pool address in a register the compiler cannot re-derive: a shared-memory address on sm_100 carries the
+    // CTA's cluster rank, so "recomputing" &pools[warp] is S2R CgaCtaId + S2R TID + 4 ALU -- and r2n's SASS did that 15
+    // times, once inside every pass of the bullet loop (25 + ~10 warp-instructions per warp-tick, two S2R latencies each).
+    WarpPool *wp = &pools[threadIdx.x >> 5];
+    asm volatile("" : "+l"(wp));
+    __builtin_assume(__isShared(wp));
+    WarpPool &w = *wp;
+#else
     WarpPool &w = pools[threadIdx.x >> 5];
+#endif
     Geo<N> g(global_warp(), ra.e_end, ra.e0);
     Lane<N> s;
     double ret0, ret1;
@@ -426,7 +436,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
             tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, false, c);
             unsigned ev; int died_ai;
             gather(g, s);  // enemy positions after the move, hp before the bullet loop
-            bullets_dense<N>(g, s, w, cnt, c, ev, died_ai);
+            bullets_dense<N, true>(g, s, w, cnt, c, ev, died_ai);
             ObsLoads<N> q;
             observe_issue<N>(p, s, q);  // positions are final; hp / alive masks are settled by then
             tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);

@@ -627,7 +627,10 @@ __device__ __forceinline__ void pool_publish_base(const Geo<N> &g, const Lane<N>
 
 // The bullets of an env that is reset vanish (self.bullets = [], battle_env.py:272): the callers drop them
 // with pool_filter() when that happens (once per game), which keeps the per-tick loop free of that test.
-template <int N>
+// BRANCHFREE: the form of the pass body.  The fused rollout is bound by instruction issue and runs the branch-free body
+// (+5.6 %); the single-tick kernel is bound by latency and is faster with the branching one (424 vs 449 us per tick at
+// 1,048,576 envs, r2n: fewer shared-memory loads in flight per pass).
+template <int N, bool BRANCHFREE>
 __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpPool &w, int &cnt, const TickCtx &c,
                                               unsigned &ev, int &died_ai) {
     const int lane = g.lane();
@@ -641,7 +644,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
     __syncwarp();
     // (the caller has run gather(): enemy positions after the move, hp before the bullet loop)
     int out = 0;
-#ifndef BS_DENSE_BRANCHY
+    if (BRANCHFREE) {
     // Branch-free body: every lane runs the advance, the base test and the N plane tests, and the outcome is assembled
     // with selects.  The chain miss / else base / else planes cost four divergent regions (BSSY / BRA / BSYNC, ~14
     // instructions per pass) that almost every pass executed anyway, since some lane of 32 always takes each side.
@@ -682,7 +685,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         }
         out += __popc(kb);
     }
-#else
+    } else {
 #pragma unroll 1
     for (int base = 0; base < cnt_in; base += 32) {
         const int idx = base + lane;
@@ -713,11 +716,9 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         const unsigned kb = __ballot_sync(FULL, keep);
         const int nidx = out + __popc(kb & lt);
         if (keep) w.ent[nidx] = make_uint2(P, M);       // nidx <= idx: never ahead of a read
-#ifndef BS_DENSE_PREDICATED
         // An overlap with a plane is rare (about one bullet per warp-tick): a warp-uniform branch around its
         // bookkeeping instead of ~20 predicated instructions in every pass (r2a: 39 of 504 per warp-tick).
         if (__any_sync(FULL, cm != 0))
-#endif
         if (cm) {                                       // (cm != 0 implies keep: the bullet flew on)
             const int eb = w.baseT[owner] >> 27;
             atomicAdd(&w.hits[eb + __ffs(cm) - 1], 1u);
@@ -726,7 +727,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         }
         out += __popc(kb);
     }
-#endif
+    }
     cnt = out;
     __syncwarp();
     ev = w.ev[lane];
