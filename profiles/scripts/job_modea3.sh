@@ -1,6 +1,8 @@
 #!/bin/bash
+# A/B of library variants on Mode A (bs_step at 65,536 / 1,048,576 envs) and the config-5 tick
+# usage: job_modea3.sh "lib_a.so lib_b.so ..."
 for rep in 1 2; do
-for lib in deep-rl-battlespace_b200/battlespace/libbattlespace.so ab/lib_branchy.so; do
+for lib in $1; do
   BATTLESPACE_LIB=$PWD/$lib python profiles/bench_configs.py modeA cfg5n 2>/dev/null | python -c "
 import sys, json
 for l in sys.stdin:
