@@ -341,12 +341,15 @@ __global__ void __launch_bounds__(STEP_BLOCK, LEAN ? STEP_MIN_BLOCKS_LEAN : STEP
     flush_tally<N>(p, tl);
 }
 
-// 128-thread blocks x 8 resident (32 warps per SM at 64 registers); 6, 7, 9 and 10 resident blocks measured slower (r1).
+// 64-thread blocks x 14 resident = 28 warps per SM at 72 registers.  Round 1 ran 128 x 8 (32 warps at 64 registers; 6, 7, 9
+// and 10 blocks all measured slower then); after the branch-free passes of round 2 the 8 extra registers (spills 36 -> 8
+// bytes, fewer IMAD.MOV) are worth more than the 4 warps: 128 x 8 1.787e10, 128 x 7 1.816e10, 64 x 14 1.821e10,
+// 32 x 28 1.806e10, 128 x 6 (80 registers) 1.776e10, 256 x 3 1.717e10 agent-steps/s (A/B on the bench command).
 #ifndef ROLLOUT_BLOCK
-#define ROLLOUT_BLOCK 128
+#define ROLLOUT_BLOCK 64
 #endif
 #ifndef ROLLOUT_MIN_BLOCKS
-#define ROLLOUT_MIN_BLOCKS (1024 / ROLLOUT_BLOCK)
+#define ROLLOUT_MIN_BLOCKS (896 / ROLLOUT_BLOCK)
 #endif
 template <int N, bool CONT>
 __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_kernel(Params p, RolloutArgs ra) {
