@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import sys
 import os
 
 import numpy as np
@@ -120,11 +121,17 @@ class parallel_env:
     # ------------------------------------------------------------------------------------------
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and not sys.is_finalizing():   # at interpreter shutdown the CUDA context may already be gone: leave it to the driver
             try:
                 lib.bs_destroy(h)
             except Exception:
                 pass
+
+    def close_handle(self):
+        """Explicit, deterministic release of the native handle (bs_destroy synchronises the device)."""
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            check(lib.bs_destroy(h))
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
