@@ -1,5 +1,5 @@
 """Small end-to-end exercise of every kernel and entry point at ragged sizes (E = 203; N = 3, 2, 8).
-(compute-sanitizer is closed on this GPU pool, so this runs plain.)"""
+Run plain, or under compute-sanitizer (profiles/scripts/job_sanitizer.sh) where the pool allows it."""
 import os, sys
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -28,6 +28,14 @@ for N, cont in ((3, True), (2, False), (8, True)):
     env.render_frame(E - 1)
     env.instinct_actions(1)
     st = env.get_state(); env.set_state(st)
+    if N <= 5:   # the team-per-thread rollout mapping and both bullet-layout converters
+        os.environ["BS_ROLLOUT_V2"] = "1"
+        env2 = parallel_env(n_agents=N, continuous_actions=cont, n_envs=E, seed=1)
+        os.environ.pop("BS_ROLLOUT_V2")
+        env2.rollout(24, "random", "instinct", 0, None, rp)
+        env2.step_batched(act)
+        env2.rollout(8, "instinct", "random", 1, None, None)
+        env2.get_state()
     torch.cuda.synchronize()
     print(N, cont, env.stats().tolist(), len(log.new_games()))
 print("exercise_all_kernels OK")
