@@ -16,6 +16,7 @@ ACT_I32, ACT_F32, ACT_F64, ACT_NONE = 0, 1, 2, 3
 POL_EXTERNAL, POL_RANDOM, POL_INSTINCT, POL_INSTINCT_FF = 0, 1, 2, 3
 WINNER_NAMES = ("none", "red", "blue", "tie")
 BULLET_SLOTS = 12
+STATIC_SCRATCH_BYTES = 8 << 20   # BS_STATIC_SCRATCH_BYTES
 POLICIES = {"external": POL_EXTERNAL, "random": POL_RANDOM, "instinct": POL_INSTINCT,
             "instinct_ff": POL_INSTINCT_FF}
 
@@ -24,7 +25,7 @@ SYMBOLS = (
     "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_reset", "bs_step", "bs_step_team",
     "bs_step_team_replay", "bs_instinct_actions", "bs_rollout_fused", "bs_stats", "bs_stats_device", "bs_get_state",
     "bs_set_state", "bs_reset_host", "bs_step_host", "bs_step_team_host", "bs_instinct_actions_host",
-    "bs_rollout_fused_host", "bs_rollout_fused_host_begin", "bs_rollout_fused_host_end", "bs_actor_forward", "bs_rollout_actor", "bs_replay_sample", "bs_render", "bs_episode_log", "bs_episode_log_count",
+    "bs_rollout_fused_host", "bs_rollout_fused_host_begin", "bs_rollout_fused_host_end", "bs_actor_forward", "bs_rollout_actor", "bs_rollout_actor_static", "bs_replay_sample", "bs_render", "bs_episode_log", "bs_episode_log_count",
 )
 
 
@@ -103,6 +104,8 @@ lib.bs_rollout_fused_host_end.argtypes = [_vp, _vp]
 lib.bs_actor_forward.argtypes = [_vp, _i, C.POINTER(bs_actor), _i, _vp, C.POINTER(bs_ou_noise), _vp, _vp]
 lib.bs_rollout_actor.argtypes = [_vp, _i, _i, C.POINTER(bs_actor), _i, _i, C.POINTER(bs_ou_noise), C.POINTER(bs_replay), _i64,
                                  _vp, _vp, _vp, _vp, _vp, _vp, _vp]
+lib.bs_rollout_actor_static.argtypes = [_vp, _i, _i, C.POINTER(bs_actor), _i, _i, C.POINTER(bs_ou_noise), C.POINTER(bs_replay), _i64,
+                                        _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_replay_sample.argtypes = [C.POINTER(bs_replay), _i, _i, _i, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
 lib.bs_render.argtypes = [_vp, _i64, C.POINTER(bs_sprites), _vp, _vp]
 lib.bs_episode_log.argtypes = [_vp, _vp, _i64]

@@ -644,6 +644,35 @@ static int obs_tables_for(int device, ObsTables *out) {
     return BS_OK;
 }
 
+// ---- static scratch of bs_rollout_actor_static (no reference counterpart; added for callers that may not allocate) ----
+// One file-scope array per loaded library image and device: every GPU that loads libbattlespace.so holds these
+// BS_STATIC_SCRATCH_BYTES until the process exits.  In HOST code the name g_static_scratch is only a stand-in for the
+// symbol, not a device address: the kernels get the pointer cudaGetSymbolAddress returns, resolved once per device with
+// that device current.  All calls on a device share the array: calls that overlap on the GPU (two streams, two handles)
+// race on it.  Nothing in it has to start at zero -- every byte a call reads was written earlier by that call (the actor
+// kernel writes all E*N*A actions before the step kernel reads them; the step kernel writes env_done[0,E) before the
+// next tick's actor kernel reads it as the OU reset mask; tick 0 uses the caller's noise->reset_mask).
+static __device__ __align__(256) unsigned char g_static_scratch[BS_STATIC_SCRATCH_BYTES];
+static unsigned char *g_static_scratch_ptr[64];
+static std::mutex g_static_scratch_mu;
+
+static int static_scratch_for(int device, unsigned char **out) {   // the caller has made `device` current
+    std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+    if (device < 0 || device >= 64) return fail(BS_E_INVALID, "device index out of range");
+    if (!g_static_scratch_ptr[device]) {
+        int cur = -1;
+        CU(cudaGetDevice(&cur));
+        if (cur != device) return fail(BS_E_CUDA, "static scratch: the handle's device is not current");
+        void *q = nullptr;
+        cudaError_t ce = cudaGetSymbolAddress(&q, g_static_scratch);
+        if (ce != cudaSuccess || !q)
+            return fail(BS_E_CUDA, std::string("cudaGetSymbolAddress(g_static_scratch): ") + cudaGetErrorString(ce));
+        g_static_scratch_ptr[device] = static_cast<unsigned char *>(q);
+    }
+    *out = g_static_scratch_ptr[device];
+    return BS_OK;
+}
+
 template <typename T>
 static int dalloc(bs_handle *h, T **ptr, size_t n) {
     void *q = nullptr;
@@ -1054,6 +1083,47 @@ int bs_rollout_actor(bs_handle *h, int T, int learner_team, const bs_actor *acto
         if ((rc = launch_step(h, sa, st))) return rc;
         aa.step += 1;
         if (noise) aa.reset_mask = env_done;  // envs that just finished start the next game with fresh noise
+    }
+    return BS_OK;
+}
+
+// bs_rollout_actor without caller work buffers and without any allocation: the action rows that travel from the
+// actor kernel to the step kernel (and env_done, when the caller does not want it) live in g_static_scratch.
+// Same kernels, same order as bs_rollout_actor, so the results are bit-identical (tests/test_zz_no_alloc.py).
+int bs_rollout_actor_static(bs_handle *h, int T, int learner_team, const bs_actor *actors, int hidden, int other_policy,
+                            const bs_ou_noise *noise, const bs_replay *replay, int64_t cursor, float *obs, float *rew,
+                            uint8_t *done, uint8_t *env_done, int8_t *winner, void *stream) {
+    if (!h) return fail(BS_E_INVALID, "null handle");
+    if (T < 1) return fail(BS_E_INVALID, "T must be >= 1");
+    if (cursor < 0) return fail(BS_E_INVALID, "cursor must be >= 0");
+    const size_t act_bytes = (size_t)h->E * h->N * h->A * sizeof(float);
+    const size_t done_off = (act_bytes + 255) & ~(size_t)255;
+    const size_t need = done_off + (env_done ? 0 : (size_t)h->E);
+    if (need > (size_t)BS_STATIC_SCRATCH_BYTES)
+        return fail(BS_E_INVALID, "bs_rollout_actor_static: n_envs*N*A*4 (+ n_envs) = " + std::to_string(need) +
+                                  " bytes of scratch exceed BS_STATIC_SCRATCH_BYTES = " + std::to_string((size_t)BS_STATIC_SCRATCH_BYTES) +
+                                  "; use bs_rollout_actor with caller buffers or a smaller handle");
+    DeviceGuard guard(h->device);
+    unsigned char *scratch = nullptr;
+    int rc = static_scratch_for(h->device, &scratch); if (rc) return rc;
+    float *act_scratch = reinterpret_cast<float *>(scratch);
+    if (!env_done) env_done = scratch + done_off;
+    ActorArgs aa;
+    if ((rc = actor_args(h, learner_team, actors, hidden, obs, noise, act_scratch, &aa))) return rc;
+    if (other_policy < BS_POL_RANDOM || other_policy > BS_POL_INSTINCT_FF) return fail(BS_E_INVALID, "other_policy must be an in-kernel policy");
+    if ((rc = replay_check(h, replay, T))) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    StepArgs sa{act_scratch, BS_ACT_F32, h->N, learner_team, {POL_EXTERNAL, POL_EXTERNAL}, nullptr, obs, rew, done, env_done, winner, {}, 0, 1};
+    sa.obs_in = obs;
+    sa.pol[1 - learner_team] = other_policy;
+    if (replay && replay->capacity > 0) sa.rp = *replay;
+    struct PdlScope { PdlScope() { g_pdl = getenv("BS_NO_PDL") == nullptr; } ~PdlScope() { g_pdl = false; } } pdl_scope;
+    for (int t = 0; t < T; ++t) {
+        if ((rc = launch_actor(h, aa, st))) return rc;
+        if (sa.rp.capacity > 0) sa.cursor_mod = (cursor + (int64_t)t * h->E) % sa.rp.capacity;
+        if ((rc = launch_step(h, sa, st))) return rc;
+        aa.step += 1;
+        if (noise) aa.reset_mask = env_done;
     }
     return BS_OK;
 }

@@ -217,6 +217,24 @@ int bs_rollout_actor(bs_handle *h, int T, int learner_team, const bs_actor *acto
                      float *obs, float *act_scratch, float *rew, uint8_t *done, uint8_t *env_done,
                      int8_t *winner, void *stream);
 
+/* bs_rollout_actor for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and bit-identical results, but there is no act_scratch argument and env_done may be NULL: the
+ * action rows [E,N,A] f32 handed from the actor kernel to the step kernel (and env_done [E] u8 when NULL) live in
+ * a file-scope `static __device__` array of BS_STATIC_SCRATCH_BYTES inside the library, which every GPU that
+ * loads the library holds until the process exits.  The call makes no cudaMalloc / cudaFree / allocating library
+ * call.  Limit: round_up(n_envs*N*A*4, 256) + (env_done ? 0 : n_envs) <= BS_STATIC_SCRATCH_BYTES (8 MiB: about
+ * 226,000 envs of 3v3 continuous); a larger handle is answered with BS_E_INVALID and a message naming both numbers.
+ * The array is shared by every call on the device and keeps the last call's contents (nothing in it needs
+ * clearing: each call writes what it reads): calls that OVERLAP on the GPU -- two streams or two handles on one
+ * device -- race on it; serialise them.  The first call on a device resolves the array's device address
+ * (cudaGetSymbolAddress); under stream capture, make one call on that device before the capture begins. */
+#define BS_STATIC_SCRATCH_BYTES (8u << 20)
+int bs_rollout_actor_static(bs_handle *h, int T, int learner_team, const bs_actor *actors, int hidden,
+                            int other_policy, const bs_ou_noise *noise, const bs_replay *replay,
+                            int64_t cursor, float *obs, float *rew, uint8_t *done, uint8_t *env_done,
+                            int8_t *winner, void *stream);
+
 /* ReplayBuffer.sample_buffer (maddpg/buffer.py:49-67) as one gather launch: idx [B] int64 device row
  * indices (the caller draws them: np.random.choice(max_mem, batch_size) with replacement, :51-52).
  * Outputs (device, float32 unless noted; any may be NULL): actor_states [N,B,L], states [B,N*L],
