@@ -217,6 +217,11 @@ __global__ void __launch_bounds__(ACTOR_BLOCK, 3) actor_kernel(ActorArgs aa) {
     // (Measured and not kept, r2f: 32-row units handed out warp by warp from a device counter, every block resident for
     // the whole launch -- the kernel alone 36.9 instead of 38.2 us, but the config-5 tick 65.9 instead of 61.6 us: blocks
     // that never exit leave no room for the next grid's blocks to start under programmatic dependent launch.)
+    // (Measured and not kept, r2v: a static, balanced split in 32-row units -- every resident block slot gets a block and
+    // the same number of units to within one, instead of 384 blocks of two tiles on 444 slots.  The kernel alone stayed
+    // at 34.8 us: it is latency-bound per warp (3 warps per scheduler, issue slots 41 % busy, FMA pipe 53 %, LSU data
+    // pipe 56 %), so its time is (units per warp) x (time per unit) = 2 units either way; the config-5 tick went from
+    // 61.6 to 67.2 us because the step kernel's blocks no longer find SMs with a free slot early.)
     for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const long long e = tile * TM + tid;
         const bool ok = e < aa.E;
