@@ -212,17 +212,13 @@ struct Lane {
 
 template <int N>
 __device__ __forceinline__ void gather(const Geo<N> &g, Lane<N> &s) {
-    // x 11 bits | y 10 bits | hp 3 bits
-    uint32_t mine = (uint32_t)s.x | ((uint32_t)s.y << 11) | ((uint32_t)(s.hp > 0 ? s.hp : 0) << 21);
-    s.am = 0; s.ehp4 = 0;
+    // positions by shuffle, the alive mask from ONE ballot; the enemies' hit points are only needed when a plane may die
+    // inside the bullet loop, and resolve_plane_hits fetches them itself then
+    const uint32_t mine = (uint32_t)s.x | ((uint32_t)s.y << 16);
 #pragma unroll
-    for (int j = 0; j < N; ++j) {
-        uint32_t v = __shfl_sync(FULL, mine, g.eb() + j);
-        s.exy[j] = (v & 0x7ffu) | (((v >> 11) & 0x3ffu) << 16);
-        uint32_t hp = (v >> 21) & 7u;
-        s.ehp4 |= hp << (4 * j);
-        s.am |= (hp ? 1u : 0u) << j;
-    }
+    for (int j = 0; j < N; ++j) s.exy[j] = __shfl_sync(FULL, mine, g.eb() + j);
+    s.am = (__ballot_sync(FULL, s.hp > 0) >> g.eb()) & ((1u << N) - 1u);
+    s.ehp4 = 0;
 }
 
 // a / b for a compile-time divisor, correctly rounded, in 3 FMA-class instructions instead of the generic
@@ -453,8 +449,10 @@ __device__ __forceinline__ long long warp_sum(long long v) {
 // [0, rx) x [0, ry).  A negative low field borrows from the high one, but then the low test has
 // already failed; a negative high field makes D huge as unsigned.  (colliderect closed forms,
 // plane -28<dx<28, -26<dy<25; base -34<dx<34, -33<dy<32.)
+// Both fields <= (rx - 1, ry - 1)  <=>  the per-halfword unsigned minimum leaves D unchanged: VIMNMX.U16x2 + ISETP
+// instead of LOP3 + 2 ISETP (rx, ry are compile-time constants at every call site; +1.2 % on the rollout, r2w).
 __device__ __forceinline__ bool rect_hit(uint32_t D, uint32_t rx, uint32_t ry) {
-    return (D & 0xffffu) < rx && D < (ry << 16);
+    return __vminu2(D, ((ry - 1u) << 16) | (rx - 1u)) == D;
 }
 constexpr uint32_t PLANE_OFF = B_BIAS - (27u | (25u << 16));  // pos - PLANE_OFF: fields x+27, y+25
 
@@ -557,7 +555,7 @@ __device__ __forceinline__ bool bullet_advance(uint32_t &P, int32_t dlt, int age
     if ((P & (0xffffu | B_XEXACT)) == 63u) P += 1u;
     if ((P & (0x1fff0000u | B_YEXACT)) == (63u << 16)) P += 0x10000u;
     const uint32_t Q = (P & B_POS) - B_BIAS;  // fields x, y (a negative one wraps to a huge unsigned value)
-    const bool miss = (Q & 0xffffu) > 1200u || Q > ((800u << 16) | 0xffffu);
+    const bool miss = __vminu2(Q, (800u << 16) | 1200u) != Q;   // a field beyond (1200, 800), negative ones included (VIMNMX.U16x2)
     return miss || age >= SLOTS;  // 12th update: dist_travelled >= 500, sprites.py:334-337
 }
 
@@ -569,6 +567,12 @@ template <int N, class CmOf, class Drop>
 __device__ __forceinline__ void resolve_plane_hits(const Geo<N> &g, Lane<N> &s, unsigned cand, unsigned &ev,
                                                    int &died_ai, CmOf cm_of, Drop drop) {
     unsigned allc = __reduce_or_sync(FULL, cand);
+    {   // the enemies' hit points before the bullet loop (gather() no longer carries them)
+        const uint32_t myhp = (uint32_t)(s.hp > 0 ? s.hp : 0);
+        s.ehp4 = 0;
+#pragma unroll
+        for (int j = 0; j < N; ++j) s.ehp4 |= __shfl_sync(FULL, myhp, g.eb() + j) << (4 * j);
+    }
     while (allc) {
         const int ai = __ffs(allc) - 1;
         allc &= allc - 1;
@@ -651,7 +655,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
 #pragma unroll 1
     for (int base = 0; base < cnt_in; base += 32) {
         const int idx = base + lane;
-        const uint2 en = w.ent[min(idx, POOL_CAP - 1)];
+        const uint2 en = w.ent[idx];                    // idx < 32 * ceil(cnt_in / 32) <= POOL_CAP (cnt_in <= POOL_CAP by construction)
         const uint32_t P0 = idx < cnt_in ? en.x : 0u;
         uint32_t M = en.y;
         const int owner = (M >> 23) & 31;
@@ -856,10 +860,13 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
 
     // ---- report sums (main.py:193-203,218-253); the env's first lane keeps them ----------------
     double r0 = 0, r1 = 0;
+    {   // each team's first lane sums its team left to right (0 + a == a exactly, so the chain starts at its own reward), then
+        // red's first lane fetches blue's total: N double shuffles instead of 2N, same additions in the same order
+        double t = rew;
 #pragma unroll
-    for (int kk = 0; kk < N; ++kk) {
-        r0 += __shfl_sync(FULL, rew, g.gb() + kk);
-        r1 += __shfl_sync(FULL, rew, g.gb() + N + kk);
+        for (int kk = 1; kk < N; ++kk) t += __shfl_sync(FULL, rew, g.tb() + kk);
+        r0 = t;
+        r1 = __shfl_sync(FULL, t, g.gb() + N);
     }
     const bool first = c.active && g.i() == 0;
     if (first) { ret0 += r0; ret1 += r1; tl.ticks += 1; }
