@@ -163,6 +163,8 @@ __device__ __forceinline__ void lane_policy_philox(const Params &p, const Geo<N>
             for (int c = 0; c < 4; ++c) raw[c] = c == adisc ? 1.0f : 0.0f;
         }
     }
+    else { adisc = 0; a[0] = a[1] = a[2] = 0; raw[0] = raw[1] = raw[2] = 0; }
+    if (CONT) raw[3] = 0;
 }
 
 // 64-thread blocks, 12 resident (24 warps per SM at 80 registers): measured 1.5 % faster than 128 x 6 in Mode A
@@ -406,11 +408,18 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
 #pragma unroll
             for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
-        int adisc = 0;
-        double a[3] = {0, 0, 0}, spread_u = 0;
-        float raw[4] = {0, 0, 0, 0};
-        if (g.valid()) {
-            if (pol == POL_EXTERNAL) {
+        // an in-kernel policy touches registers only: the warp's idle lanes run it too, which saves the defaults
+        // (13 moves) and the divergent region that every warp pays for its two spare lanes
+        int adisc;
+        double a[3], spread_u;
+        float raw[4];
+        if (pol != POL_EXTERNAL) {
+            lane_policy_philox<N, CONT>(p, g, s, pol, o, adisc, a, spread_u, raw);
+        } else {
+            adisc = 0; a[0] = a[1] = a[2] = 0; spread_u = 0; raw[0] = raw[1] = raw[2] = raw[3] = 0;
+        }
+        if (g.valid() && pol == POL_EXTERNAL) {
+            {
                 const float *src = ra.ext + (((long long)t * p.E + g.e()) * N + g.k()) * A;
                 if (CONT) {
 #pragma unroll
@@ -424,8 +433,6 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
                 env_philox(p, g.e(), s.episode, s.tick, g.i(), PURPOSE_AGENT_TICK, w4);
                 agent_tick_units(w4, u);
                 spread_u = u[4];
-            } else {
-                lane_policy_philox<N, CONT>(p, g, s, pol, o, adisc, a, spread_u, raw);
             }
         }
         if (writer && ra.rp.action) {  // the action row is complete before the tick: write it now

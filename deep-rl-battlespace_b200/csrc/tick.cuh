@@ -246,8 +246,8 @@ template <int N>
 struct ObsLoads {
     double r[N + 1];   // atan2(|dy|, dx) of the pair
     float od[N + 1];
-    unsigned neg;      // bit k: dy < 0 for pair k, i.e. atan2(dy, dx) = -r[k] (atan2 is odd in y; the host
-                       // verifies that its libm honours this bit for bit when it builds the table)
+    // (dy < 0 for a pair means atan2(dy, dx) = -r[k]: atan2 is odd in y, and the host verifies that its libm honours
+    // this bit for bit when it builds the table; observe_finish takes the sign from the positions)
 };
 
 __device__ __forceinline__ void pair_load(const Params &p, int dx, int dy, double &r, float &od) {
@@ -282,13 +282,11 @@ __device__ __forceinline__ void observe_issue(const Params &p, const Lane<N> &s,
     // are this path's scarcest resource -- ~1/3 of them used to be issued for dead planes.
     const bool me = s.hp > 0;
     q.r[0] = 0; q.od[0] = 0;
-    q.neg = s.y - s.eby < 0 ? 1u : 0u;
     if (me) pair_load(p, s.x - s.ebx, s.y - s.eby, q.r[0], q.od[0]);
 #pragma unroll
     for (int j = 0; j < N; ++j) {
         q.r[j + 1] = 0; q.od[j + 1] = 0;
         const int dy = s.y - (int)(s.exy[j] >> 16);
-        q.neg |= (dy < 0 ? 1u : 0u) << (j + 1);
         if (me && ((s.am >> j) & 1u)) pair_load(p, s.x - (int)(s.exy[j] & 0xffffu), dy, q.r[j + 1], q.od[j + 1]);
     }
 }
@@ -301,8 +299,12 @@ __device__ __forceinline__ void observe_finish(const Lane<N> &s, const ObsLoads<
     // selects: `seen ? pair_angle(..) : -1` made the compiler put a divergent region around every pair (r2l: 18
     // control-flow instructions per warp-tick here)
     float ang[N + 1];
+    // the sign of dy again from the positions (still in registers: nothing moves after the planes' move) instead of
+    // packing N + 1 sign bits before the bullet pass and unpacking them here
+    ang[0] = pair_angle(q.r[0], s.y < s.eby, s.dir);
+    const uint32_t ythr = ((uint32_t)s.y << 16) | 0xffffu;
 #pragma unroll
-    for (int j = 0; j <= N; ++j) ang[j] = pair_angle(q.r[j], (q.neg >> j) & 1u, s.dir);
+    for (int j = 0; j < N; ++j) ang[j + 1] = pair_angle(q.r[j + 1], s.exy[j] > ythr, s.dir);   // enemy y > own y
     o[0] = me ? q.od[0] : -1.0f; o[1] = me ? ang[0] : -1.0f;
 #pragma unroll
     for (int j = 0; j < N; ++j) {
