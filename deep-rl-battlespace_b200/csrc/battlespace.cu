@@ -379,9 +379,13 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
     float o[L];
     observe<N>(p, s, o);
     Tally tl;
-    const int pol = g.team() ? ra.pol[1] : ra.pol[0];  // (a dynamic index would make the compiler copy the parameter struct to local memory:
-                                                      //  r1o spent 9 % of its stall samples on those reloads)
     const bool writer = g.valid() && g.team() == ra.learner && ra.rp.capacity > 0;
+    // which ring arrays this lane writes, decided once: the tick loop tests one bit instead of re-deriving `writer` and
+    // null-checking five 64-bit pointers every tick
+    unsigned wf = 0;
+    if (writer) wf = (ra.rp.state ? 1u : 0u) | (ra.rp.action ? 2u : 0u) | (ra.rp.new_state ? 4u : 0u) | (ra.rp.reward ? 8u : 0u) | (ra.rp.done ? 16u : 0u);
+    wf |= (unsigned)(g.team() ? ra.pol[1] : ra.pol[0]) << 8;   // the lane's policy rides in the same register
+    asm volatile("" : "+r"(wf));   // (keep it in its register: the compiler would rather recompute it)
     // ring row of this lane's env at tick t (replay_check: capacity * N < 2^31, so 32-bit indices address every array)
     uint32_t row = 0;
     if (ra.rp.capacity > 0) row = (uint32_t)((ra.cursor_mod + g.e() % ra.rp.capacity) % ra.rp.capacity);
@@ -389,6 +393,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
 
 #pragma unroll 1
     for (int t = 0; t < ra.T; ++t) {
+        const int pol = (int)(wf >> 8);
         // auto-reset: the game loop's env.reset() -- main.py:148
         const bool need = g.valid() && s.env_done;
         if (__any_sync(FULL, need)) {
@@ -403,7 +408,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
             }
         }
         const uint32_t ra_i = row * N + g.k();   // this plane's slot of the row
-        if (writer && ra.rp.state) {
+        if (wf & 1u) {
             float *dst = ra.rp.state + (size_t)ra_i * L;
 #pragma unroll
             for (int c = 0; c < L; ++c) dst[c] = o[c];
@@ -435,7 +440,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
                 spread_u = u[4];
             }
         }
-        if (writer && ra.rp.action) {  // the action row is complete before the tick: write it now
+        if (wf & 2u) {
             float *dst = ra.rp.action + (size_t)ra_i * A;
 #pragma unroll
             for (int c = 0; c < A; ++c) dst[c] = raw[c];
@@ -452,15 +457,13 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
             tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
             observe_finish<N>(s, q, o);
         }
-        if (writer) {
-            if (ra.rp.new_state) {
-                float *dst = ra.rp.new_state + (size_t)ra_i * L;
+        if (wf & 4u) {
+            float *dst = ra.rp.new_state + (size_t)ra_i * L;
 #pragma unroll
-                for (int c = 0; c < L; ++c) dst[c] = o[c];
-            }
-            if (ra.rp.reward) ra.rp.reward[ra_i] = (float)rew;
-            if (ra.rp.done) ra.rp.done[ra_i] = (uint8_t)(s.env_done || s.hp <= 0);
+            for (int c = 0; c < L; ++c) dst[c] = o[c];
         }
+        if (wf & 8u) ra.rp.reward[ra_i] = (float)rew;
+        if (wf & 16u) ra.rp.done[ra_i] = (uint8_t)(s.env_done || s.hp <= 0);
         row += emod32;                       // (row, emod32 < capacity <= 2^31 / N: no 32-bit overflow)
         if (row >= cap32) row -= cap32;
     }
