@@ -421,11 +421,10 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
         if (pol != POL_EXTERNAL) {
             lane_policy_philox<N, CONT>(p, g, s, pol, o, adisc, a, spread_u, raw);
         } else {
-            adisc = 0; a[0] = a[1] = a[2] = 0; spread_u = 0; raw[0] = raw[1] = raw[2] = raw[3] = 0;
-        }
-        if (g.valid() && pol == POL_EXTERNAL) {
-            {
-                const float *src = ra.ext + (((long long)t * p.E + g.e()) * N + g.k()) * A;
+            {   // (an idle lane reads the row of the launch's first env: always there, never used)
+                adisc = 0; raw[3] = 0;
+                if (!CONT) a[0] = a[1] = a[2] = 0;
+                const float *src = ra.ext + (((long long)t * p.E + (g.valid() ? g.e() : ra.e0)) * N + g.k()) * A;
                 if (CONT) {
 #pragma unroll
                     for (int c = 0; c < 3; ++c) { a[c] = clip1((double)src[c]); raw[c] = (float)a[c]; }

@@ -385,9 +385,11 @@ static __device__ __noinline__ double2 cos_sin_dir(double dir) {
 constexpr float FLOOR_GUARD = 2.5e-4f;
 
 __device__ __forceinline__ void cos_sin_fast(double dir, float &cs, float &sn) {
-    double rad = -(dir * KC_DEG2RAD);    // dir in [-4, 364]: rad in [-6.36, 0.07]
-    if (rad < -KC_PI) rad += KC_TWO_PI;  // -> [-pi, pi]
-    const float r = (float)rad;
+    // the wrap into [-pi, pi] in float: the argument then carries float(rad) 2.4e-7 + the float add 1.2e-7 + float(2 pi)
+    // 1.75e-7 = 5.4e-7 instead of 1.9e-7, i.e. cos / sin within 9.6e-7 and the product with <= 45 within 4.3e-5 px:
+    // FLOOR_GUARD is still 5.8x that
+    float r = (float)(-(dir * KC_DEG2RAD));   // dir in [-4, 364]: rad in [-6.36, 0.07]
+    if (r < -3.14159265f) r += 6.28318531f;
     cs = __cosf(r); sn = __sinf(r);
 }
 
@@ -616,6 +618,7 @@ struct WarpPool {
     uint2 ent[POOL_CAP];         // .x = pos word, .y = meta word: the HBM layout, moved with 64-bit accesses
     uint32_t ev[32], cand[32];   // per owner lane: event codes / candidate ages of this tick
     uint32_t hits[32];           // per plane lane: bullets whose first overlapped plane (alive at the start of the loop) it is
+    uint32_t lastai[32];         // per plane lane: the largest age index among those bullets (the one that lands last)
     uint32_t candt[SLOTS][32];   // per (age index, owner): pool index << 8 | overlap mask
     uint32_t plane[32];          // x | y << 16 of every lane's plane after the move (0x7fff7fff: not alive)
     uint32_t baseT[32];          // enemy-base test word | first lane of the enemy team << 27
@@ -685,6 +688,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         if (__any_sync(FULL, cm != 0)) {                // an overlap with a plane is rare: about one bullet per warp-tick
             if (cm) {
                 atomicAdd(&w.hits[eb + __ffs(cm) - 1], 1u);
+                atomicMax(&w.lastai[eb + __ffs(cm) - 1], (unsigned)ai);
                 atomicOr(&w.cand[owner], 1u << ai);
                 w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm;
             }
@@ -728,6 +732,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         if (cm) {                                       // (cm != 0 implies keep: the bullet flew on)
             const int eb = w.baseT[owner] >> 27;
             atomicAdd(&w.hits[eb + __ffs(cm) - 1], 1u);
+            atomicMax(&w.lastai[eb + __ffs(cm) - 1], (unsigned)ai);
             atomicOr(&w.cand[owner], 1u << ai);
             w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm;
         }
@@ -744,8 +749,15 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
     // Phase 2.  The order of the list only matters when a plane can die inside this tick: if every plane is
     // overlapped by fewer bullets than it has hit points, self.agents does not change during the loop and
     // every candidate hits the first plane it overlaps (battle_env.py:348-360), whatever the order.
-    if (!__any_sync(FULL, s.hp > 0 && nh >= s.hp)) {
-        s.hp -= nh;                                     // (stays > 0; a dead plane collects no hits: it is off the field)
+    // ... and it does not matter either when a plane takes EXACTLY as many hits as it has hit points: the bullets counted
+    // in hits[] are those whose first overlapped plane it is, all of them land while it is still alive, the last one in
+    // list order -- the youngest, lastai[] -- kills it, and no bullet is left over to pass through the wreck.  Only a
+    // plane with MORE overlapping bullets than hit points needs the ordered pass (a few per cent of the deaths).
+    int la = 0;
+    if (nh) { la = (int)w.lastai[lane]; w.lastai[lane] = 0; }
+    if (!__any_sync(FULL, s.hp > 0 && nh > s.hp)) {
+        s.hp -= nh;                                     // (a dead plane collects no hits: it is off the field)
+        if (nh && s.hp <= 0) died_ai = la;
         unsigned cc = cand;
         while (cc) {
             const int ai = __ffs(cc) - 1;
@@ -758,6 +770,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
             [&](int ai) { return w.candt[ai][lane] & 0xffu; },
             [&](int ai) { w.ent[w.candt[ai][lane] >> 8].x = 0; });
     }
+    s.am = (__ballot_sync(FULL, s.hp > 0) >> g.eb()) & ((1u << N) - 1u);   // a plane may have died on the unordered path
 }
 
 // HBM <-> shared memory: the pool has the same layout in both, so a launch copies `cnt` packed entries
@@ -777,7 +790,7 @@ __device__ __forceinline__ void pool_load(const Params &p, long long gw, bool wv
     for (int q = 0; q < POOL_SPEC; ++q)
         if (q * 32 + lane < cnt) w.ent[q * 32 + lane] = v[q];
     for (int idx = POOL_SPEC * 32 + lane; idx < cnt; idx += 32) w.ent[idx] = src[idx];
-    w.ev[lane] = 0; w.cand[lane] = 0; w.hits[lane] = 0;
+    w.ev[lane] = 0; w.cand[lane] = 0; w.hits[lane] = 0; w.lastai[lane] = 0;
     __syncwarp();
 }
 
@@ -821,6 +834,17 @@ __device__ __forceinline__ void tick_end(const Params &p, const Geo<N> &g, Lane<
     // by the event code.
     if (!__any_sync(FULL, died_ai >= 0)) {
         unsigned e2 = ev;
+        {   // The two oldest events without a loop: a lane rarely has more in one tick, 0.0 + a == a and a + b == b + a
+            // exactly, so up to two terms need no ordering; the loop below only runs for a third one.
+            const int sh1 = e2 ? ((__ffs(e2) - 1) & ~1) : 0;
+            const double ra = p.r_code[(e2 >> sh1) & 3u];
+            e2 &= ~(3u << sh1);
+            const int sh2 = e2 ? ((__ffs(e2) - 1) & ~1) : 0;
+            const double rb = p.r_code[(e2 >> sh2) & 3u];
+            e2 &= ~(3u << sh2);
+            rew = (rew + ra) + rb;
+        }
+        if (__any_sync(FULL, e2 != 0))
         while (e2 != 0) {
             const int sh = (__ffs(e2) - 1) & ~1;
             rew += p.r_code[(e2 >> sh) & 3u];
