@@ -176,12 +176,12 @@ __device__ __forceinline__ void lane_policy_philox(const Params &p, const Geo<N>
 #define STEP_MIN_BLOCKS (768 / STEP_BLOCK)
 #endif
 #ifndef STEP_MIN_BLOCKS_LEAN
-#define STEP_MIN_BLOCKS_LEAN (1024 / STEP_BLOCK)
+#define STEP_MIN_BLOCKS_LEAN (896 / STEP_BLOCK)
 #endif
 // LEAN = plain bs_step (Mode A): both teams' actions from the caller, no replay rows, no auto-reset, no in-kernel policy,
 // no obs_in.  The general kernel needs 80 registers (24 resident warps per SM); without those paths the same tick fits
-// the register budget of 32 resident warps, which is what this latency-bound kernel lacks (profiles/r2a_step_raw.txt:
-// issue slots 55 % busy, 3.5 warps per issue waiting on memory).
+// 72 registers / 28 resident warps with no spill (r2y: 418 us at 1,048,576 envs; squeezed into 64 registers / 32 warps it
+// took 422 us, into 56 or 48 registers -- 36 / 40 warps, 28 / 92 bytes of spills -- 582 / 576 us).
 template <int N, bool CONT, bool LEAN>
 __global__ void __launch_bounds__(STEP_BLOCK, LEAN ? STEP_MIN_BLOCKS_LEAN : STEP_MIN_BLOCKS) step_kernel(Params p, StepArgs sa) {
     constexpr int P = 2 * N, L = 3 * N + 2;
@@ -195,9 +195,27 @@ __global__ void __launch_bounds__(STEP_BLOCK, LEAN ? STEP_MIN_BLOCKS_LEAN : STEP
     // completed; the next grid may be scheduled as soon as every block of this one has started
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;");
-    load_lane(p, g, s, ret0, ret1);
     int cnt;
-    pool_load(p, gw, gw < p.W, g.lane(), w, cnt);
+    // every load of the prologue is issued before the first one is waited for: state, pool entries + count, and (plain
+    // bs_step with float actions) the lane's action words -- one memory round trip instead of three
+    float araw[4] = {0, 0, 0, 0};
+    const bool early_act = LEAN && sa.dtype == ACT_F32 && sa.actions != nullptr;   // kernel-uniform
+    {
+        LaneRaw lr;
+        uint2 pv[POOL_SPEC_N];
+        lane_fetch(p, g, lr);
+        pool_fetch(p, gw, gw < p.W, g.lane(), pv, cnt);
+        {   // (no branch, so that the compiler keeps these loads with the others: without float actions they read the first
+            //  words of the observation table, which is always there, and the result is not used)
+            constexpr int A = CONT ? 3 : 4;
+            const long long idx = (g.valid() ? g.e() : 0) * sa.act_agents + (sa.act_agents == P ? g.i() : g.k());
+            const float *ap = early_act ? (const float *)sa.actions + idx * A : (const float *)p.obs_tab;
+#pragma unroll
+            for (int c = 0; c < A; ++c) araw[c] = ap[c];
+        }
+        lane_unpack(g, lr, s, ret0, ret1);
+        pool_commit(p, gw, gw < p.W, g.lane(), pv, w, cnt);
+    }
     pool_publish_base<N>(g, s, w);
     // (Measured and not kept, r2i: one prefetch.global.L2 per lane for the lines of the block that will take over this
     // block's slot -- 431.9 vs 431.2 us at 1,048,576 envs: the wait on the first loads is not the DRAM leg.)
@@ -229,11 +247,11 @@ __global__ void __launch_bounds__(STEP_BLOCK, LEAN ? STEP_MIN_BLOCKS_LEAN : STEP
             if (sa.dtype == ACT_I32) adisc = ((const int32_t *)sa.actions)[idx];
             else {
 #pragma unroll
-                for (int c = 0; c < 4; ++c) raw[c] = ((const float *)sa.actions)[idx * 4 + c];
+                for (int c = 0; c < 4; ++c) raw[c] = early_act ? araw[c] : ((const float *)sa.actions)[idx * 4 + c];
             }
         } else if (sa.dtype == ACT_F32) {
 #pragma unroll
-            for (int c = 0; c < 3; ++c) a[c] = (double)((const float *)sa.actions)[idx * 3 + c];
+            for (int c = 0; c < 3; ++c) a[c] = (double)(early_act ? araw[c] : ((const float *)sa.actions)[idx * 3 + c]);
         } else {
 #pragma unroll
             for (int c = 0; c < 3; ++c) a[c] = ((const double *)sa.actions)[idx * 3 + c];

@@ -777,6 +777,26 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
 // (coalesced 8-byte words), not 24 ring words per lane.  gw = global warp index = first env / K.
 // wvalid: the warp owns envs of this launch (the last block's spare warps, and in a chunked launch the
 // warps past the chunk, must neither read nor write a pool).
+// pool_load() in two halves (see lane_fetch): the loads of the count and of the first POOL_SPEC x 32 entries, then the rest
+constexpr int POOL_SPEC_N = 4;
+__device__ __forceinline__ void pool_fetch(const Params &p, long long gw, bool wvalid, int lane, uint2 (&v)[POOL_SPEC_N], int &cnt) {
+    const uint2 *src = p.pool + (wvalid ? gw : 0) * POOL_CAP;
+#pragma unroll
+    for (int q = 0; q < POOL_SPEC_N; ++q) v[q] = src[q * 32 + lane];
+    cnt = p.pool_cnt[wvalid ? gw : 0];
+}
+__device__ __forceinline__ void pool_commit(const Params &p, long long gw, bool wvalid, int lane, const uint2 (&v)[POOL_SPEC_N], WarpPool &w, int &cnt) {
+    if (!wvalid) cnt = 0;
+    const uint2 *src = p.pool + (wvalid ? gw : 0) * POOL_CAP;
+#pragma unroll
+    for (int q = 0; q < POOL_SPEC_N; ++q)
+        if (q * 32 + lane < cnt) w.ent[q * 32 + lane] = v[q];
+#pragma unroll 1
+    for (int idx = POOL_SPEC_N * 32 + lane; idx < cnt; idx += 32) w.ent[idx] = src[idx];
+    w.ev[lane] = 0; w.cand[lane] = 0; w.hits[lane] = 0; w.lastai[lane] = 0;
+    __syncwarp();
+}
+
 __device__ __forceinline__ void pool_load(const Params &p, long long gw, bool wvalid, int lane, WarpPool &w, int &cnt) {
     // The first POOL_SPEC entries are fetched without waiting for the count (the slots always exist), so
     // that count, entries and the caller's other state loads share ONE memory round trip.
@@ -948,6 +968,48 @@ __device__ __forceinline__ void reset_lane(const Params &p, const Geo<N> &g, Lan
 }
 
 // ---- state <-> registers / shared ring --------------------------------------------------------
+// The same in two halves for the single-tick kernel, which lives for one tick and is bound by the latency of exactly
+// these loads: lane_fetch() only ISSUES them (no divergent region: an idle lane reads env 0's words and discards
+// them), so that the pool entries and the caller's actions can be requested in the same memory round trip before
+// lane_unpack() waits for the first word.  (r2y: the region around load_lane() made the unpacking -- and its wait --
+// precede the pool loads, and those precede the action loads: three DRAM round trips in a row.)
+struct LaneRaw {
+    uint32_t pos, eb, m, ep;
+    double dir, r0, r1;
+    int hp, bo, be;
+};
+
+template <int N>
+__device__ __forceinline__ void lane_fetch(const Params &p, const Geo<N> &g, LaneRaw &r) {
+    constexpr int P = 2 * N;
+    const bool v = g.valid();
+    const long long e = v ? g.e() : 0;
+    const long long a = e * P + g.i();
+    r.pos = p.plane_pos[a];
+    r.dir = p.plane_dir[a];
+    r.hp = p.plane_hp[a];
+    r.eb = p.base_pos[e * 2 + (1 - g.team())];
+    r.bo = p.base_hp[e * 2 + g.team()];
+    r.be = p.base_hp[e * 2 + (1 - g.team())];
+    r.m = p.meta[e];
+    r.ep = p.episode[e];
+    r.r0 = p.ret[e * 2]; r.r1 = p.ret[e * 2 + 1];
+}
+
+template <int N>
+__device__ __forceinline__ void lane_unpack(const Geo<N> &g, const LaneRaw &r, Lane<N> &s, double &ret0, double &ret1) {
+    const bool v = g.valid();
+    s.x = v ? (int)(r.pos & 0xffff) : 0; s.y = v ? (int)(r.pos >> 16) : 0;
+    s.dir = v ? r.dir : 0.0;
+    s.hp = v ? r.hp : 0;
+    s.ebx = v ? (int)(r.eb & 0xffff) : 64; s.eby = v ? (int)(r.eb >> 16) : 64;
+    s.bhp_own = v ? r.bo : 0; s.bhp_enemy = v ? r.be : 0;
+    s.tick = v ? (int)(r.m & 0xfff) : 0; s.env_done = v ? (int)((r.m >> 16) & 0xff) : 1; s.winner = v ? (int)((r.m >> 24) & 0xff) : 0;
+    s.episode = v ? r.ep : 0u;
+    const bool first = v && g.i() == 0;
+    ret0 = first ? r.r0 : 0.0; ret1 = first ? r.r1 : 0.0;
+}
+
 template <int N>
 __device__ __forceinline__ void load_lane(const Params &p, const Geo<N> &g, Lane<N> &s, double &ret0, double &ret1) {
     constexpr int P = 2 * N;
