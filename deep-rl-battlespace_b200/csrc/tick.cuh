@@ -636,10 +636,10 @@ __device__ __forceinline__ void pool_publish_base(const Geo<N> &g, const Lane<N>
 
 // The bullets of an env that is reset vanish (self.bullets = [], battle_env.py:272): the callers drop them
 // with pool_filter() when that happens (once per game), which keeps the per-tick loop free of that test.
-// BRANCHFREE: the form of the pass body.  The fused rollout is bound by instruction issue and runs the branch-free body
-// (+5.6 %); the single-tick kernel is bound by latency and is faster with the branching one (424 vs 449 us per tick at
-// 1,048,576 envs, r2n: fewer shared-memory loads in flight per pass).
-template <int N, bool BRANCHFREE>
+// The pass body is branch-free.  The fused rollout is bound by instruction issue (+5.6 % when the branches went); the
+// single-tick kernel preferred the branching form while it ran at 64 registers (424 vs 449 us per tick at 1,048,576 envs,
+// r2n) and no longer does at 72 (403.9 vs 406.0 us, r2y), so the branching copy is gone.
+template <int N>
 __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpPool &w, int &cnt, const TickCtx &c,
                                               unsigned &ev, int &died_ai) {
     const int lane = g.lane();
@@ -653,7 +653,7 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
     __syncwarp();
     // (the caller has run gather(): enemy positions after the move, hp before the bullet loop)
     int out = 0;
-    if (BRANCHFREE) {
+    {
     // Branch-free body: every lane runs the advance, the base test and the N plane tests, and the outcome is assembled
     // with selects.  The chain miss / else base / else planes cost four divergent regions (BSSY / BRA / BSYNC, ~14
     // instructions per pass) that almost every pass executed anyway, since some lane of 32 always takes each side.
@@ -692,49 +692,6 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
                 atomicOr(&w.cand[owner], 1u << ai);
                 w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm;
             }
-        }
-        out += __popc(kb);
-    }
-    } else {
-#pragma unroll 1
-    for (int base = 0; base < cnt_in; base += 32) {
-        const int idx = base + lane;
-        uint2 en = make_uint2(0u, 0u);
-        if (idx < cnt_in) en = w.ent[idx];
-        uint32_t P = en.x, M = en.y;
-        const int owner = (M >> 23) & 31;
-        const int age = (int)(M >> 28) + 1;             // updates including this one
-        const int ai = SLOTS - age;                     // age index, 0 = oldest
-        bool keep = (P & B_VALID) != 0;                 // dead entries (plane hits of the last tick) are squeezed out
-        unsigned cm = 0;
-        if (keep && ((runmask >> owner) & 1u)) {        // the bullets of an env that did not run this tick stay put
-            const uint32_t bt = w.baseT[owner];
-            unsigned code = 0;
-            if (bullet_advance(P, meta_dlt(M), age)) code = 1u;
-            else if (rect_hit((P & B_POS) - (bt & 0x07ffffffu), 67u, 64u)) code = 2u;
-            else {
-                const uint32_t Pp = (P & B_POS) - PLANE_OFF;
-                const int eb = bt >> 27;
-#pragma unroll
-                for (int j = 0; j < N; ++j) {
-                    cm |= (rect_hit(Pp - w.plane[eb + j], 55u, 50u) ? 1u : 0u) << j;
-                }
-                M += 1u << 28;
-            }
-            if (code) { atomicOr(&w.ev[owner], code << (2 * ai)); keep = false; }
-        }
-        const unsigned kb = __ballot_sync(FULL, keep);
-        const int nidx = out + __popc(kb & lt);
-        if (keep) w.ent[nidx] = make_uint2(P, M);       // nidx <= idx: never ahead of a read
-        // An overlap with a plane is rare (about one bullet per warp-tick): a warp-uniform branch around its
-        // bookkeeping instead of ~20 predicated instructions in every pass (r2a: 39 of 504 per warp-tick).
-        if (__any_sync(FULL, cm != 0))
-        if (cm) {                                       // (cm != 0 implies keep: the bullet flew on)
-            const int eb = w.baseT[owner] >> 27;
-            atomicAdd(&w.hits[eb + __ffs(cm) - 1], 1u);
-            atomicMax(&w.lastai[eb + __ffs(cm) - 1], (unsigned)ai);
-            atomicOr(&w.cand[owner], 1u << ai);
-            w.candt[ai][owner] = ((uint32_t)nidx << 8) | cm;
         }
         out += __popc(kb);
     }
