@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(STEP_BLOCK, LEAN ? STEP_MIN_BLOCKS_LEAN : STEP
         gather(g, s);  // enemy positions after the move, hp before the bullet loop
         if (want_obs) observe_issue<N>(p, s, q);
         unsigned ev; int died_ai;
-        bullets_dense<N>(g, s, w, cnt, c, ev, died_ai);
+        bullets_dense<N, false>(g, s, w, cnt, c, ev, died_ai);
         tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);
         if (want_obs) observe_finish<N>(s, q, o);
     }
@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(ROLLOUT_BLOCK, ROLLOUT_MIN_BLOCKS) rollout_ker
             tick_begin<N, CONT>(p, g, s, adisc, a, spread_u, false, c);
             unsigned ev; int died_ai;
             gather(g, s);  // enemy positions after the move, hp before the bullet loop
-            bullets_dense<N>(g, s, w, cnt, c, ev, died_ai);
+            bullets_dense<N, true>(g, s, w, cnt, c, ev, died_ai);
             ObsLoads<N> q;
             observe_issue<N>(p, s, q);  // positions are final; hp / alive masks are settled by then
             tick_end<N>(p, g, s, c, ev, died_ai, rew, ret0, ret1, tl);

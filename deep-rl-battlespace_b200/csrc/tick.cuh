@@ -618,8 +618,6 @@ struct WarpPool {
     uint2 ent[POOL_CAP];         // .x = pos word, .y = meta word: the HBM layout, moved with 64-bit accesses
     uint32_t ev[32], cand[32];   // per owner lane: event codes / candidate ages of this tick
     uint32_t hits[32];           // per plane lane: bullets whose first overlapped plane (alive at the start of the loop) it is
-    uint32_t sink[32];           // target of the event atomic for lanes without an event (value 0: never read)
-    uint2 sink2[32];             // the same for the spawn store of lanes that do not shoot
     uint32_t lastai[32];         // per plane lane: the largest age index among those bullets (the one that lands last)
     uint32_t candt[SLOTS][32];   // per (age index, owner): pool index << 8 | overlap mask
     uint32_t plane[32];          // x | y << 16 of every lane's plane after the move (0x7fff7fff: not alive)
@@ -641,7 +639,10 @@ __device__ __forceinline__ void pool_publish_base(const Geo<N> &g, const Lane<N>
 // The pass body is branch-free.  The fused rollout is bound by instruction issue (+5.6 % when the branches went); the
 // single-tick kernel preferred the branching form while it ran at 64 registers (424 vs 449 us per tick at 1,048,576 envs,
 // r2n) and no longer does at 72 (403.9 vs 406.0 us, r2y), so the branching copy is gone.
-template <int N>
+// SINK: the three places where a lane may have nothing to publish (no spawn, no event, no hit) run without a divergent
+// region, non-publishing lanes writing a harmless value to a harmless place.  +1.3 % on the issue-bound fused rollout; the latency-bound
+// single-tick kernel is faster with the branches (410.0 vs 414.3 us at 1,048,576 envs, 35.2 vs 37.2 us at 65,536).
+template <int N, bool SINK>
 __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpPool &w, int &cnt, const TickCtx &c,
                                               unsigned &ev, int &died_ai) {
     const int lane = g.lane();
@@ -650,8 +651,11 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
     w.plane[lane] = s.hp > 0 ? ((uint32_t)s.x | ((uint32_t)s.y << 16)) : 0x7fff7fffu;
     const unsigned runmask = __ballot_sync(FULL, c.run);
     const unsigned sp = __ballot_sync(FULL, c.spawnP != 0);
-    // (a lane without a spawn stores into its own sink slot: no divergent region, +0.7 %)
-    *(c.spawnP ? &w.ent[cnt + __popc(sp & lt)] : &w.sink2[lane]) = make_uint2(c.spawnP, pack_meta(c.spawnD, lane, 0));
+    // (sink of the spawn store: the last slot of the pool, which is free whenever some lane does not spawn -- 32 x 11 survivors
+    //  + the spawns fill it exactly; the dead word written there is beyond cnt_in.  Sink of the event atomic: the lane's own ev word,
+    //  OR-ing 0 changes nothing.)
+    if (SINK) *(c.spawnP ? &w.ent[cnt + __popc(sp & lt)] : &w.ent[POOL_CAP - 1]) = make_uint2(c.spawnP, pack_meta(c.spawnD, lane, 0));
+    else if (c.spawnP) w.ent[cnt + __popc(sp & lt)] = make_uint2(c.spawnP, pack_meta(c.spawnD, lane, 0));
     const int cnt_in = cnt + __popc(sp);
     __syncwarp();
     // (the caller has run gather(): enemy positions after the move, hp before the bullet loop)
@@ -683,7 +687,8 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
         const unsigned code = act ? (miss ? 1u : (hitb ? 2u : 0u)) : 0u;
         if (!act || code) cm = 0;
         if (!act) P = P0; else if (!code) M += 1u << 28;
-        atomicOr(code ? &w.ev[owner] : &w.sink[lane], code << (2 * ai));   // no divergent region: a bullet without an event ORs 0 into its lane's sink (+0.4 %)
+        if (SINK) atomicOr(&w.ev[code ? owner : lane], code << (2 * ai));   // a bullet without an event ORs 0 into its lane's own word
+        else if (code) atomicOr(&w.ev[owner], code << (2 * ai));
         const bool keep = live && !code;
         const unsigned kb = __ballot_sync(FULL, keep);
         const int nidx = out + __popc(kb & lt);
@@ -713,7 +718,8 @@ __device__ __forceinline__ void bullets_dense(const Geo<N> &g, Lane<N> &s, WarpP
     // in hits[] are those whose first overlapped plane it is, all of them land while it is still alive, the last one in
     // list order -- the youngest, lastai[] -- kills it, and no bullet is left over to pass through the wreck.  Only a
     // plane with MORE overlapping bullets than hit points needs the ordered pass (a few per cent of the deaths).
-    int la = (int)w.lastai[lane]; w.lastai[lane] = 0;   // (on every lane: cheaper than a divergent region around it)
+    int la = 0;
+    if (SINK || nh) { la = (int)w.lastai[lane]; w.lastai[lane] = 0; }
     if (!__any_sync(FULL, s.hp > 0 && nh > s.hp)) {
         s.hp -= nh;                                     // (a dead plane collects no hits: it is off the field)
         if (nh && s.hp <= 0) died_ai = la;
